@@ -1,0 +1,200 @@
+"""ctypes binding of libfcp.so (C ABI in include/fcp.h).
+
+There is no CPU fallback: if the library is missing, ``lib()`` raises.  The
+library is built in-tree by ``dlrover_wuqiong_b200.csrc.build`` so that the
+``.so`` travels with the source tree.
+"""
+import ctypes
+import errno
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libfcp.so")
+
+REGION_BYTES = 16384
+DEFAULT_CHUNK_BYTES = 2 << 20
+SUM_NONE, SUM_CRC32C = 0, 1
+MODE_STAGED, MODE_DIRECT = 0, 1
+
+# struct fcp_desc { const void* ptr; uint64_t dst_off; uint64_t nbytes; }
+DESC_DTYPE = np.dtype([("ptr", "<u8"), ("dst_off", "<u8"), ("nbytes", "<u8")])
+
+# every symbol include/fcp.h declares: (name, restype, argtypes)
+_vp, _u64, _u32, _i = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int
+SYMBOLS = [
+    ("fcp_version", _i, []),
+    ("fcp_last_error", ctypes.c_char_p, []),
+    ("fcp_init", _i, [_i]),
+    ("fcp_plan_create", _i, [_vp, _u64, _u64, _u32, _i, ctypes.POINTER(_vp)]),
+    ("fcp_plan_update_ptrs", _i, [_vp, _vp, _u64]),
+    ("fcp_plan_destroy", None, [_vp]),
+    ("fcp_plan_total_bytes", _u64, [_vp]),
+    ("fcp_plan_num_chunks", _u64, [_vp]),
+    ("fcp_plan_num_regions", _u64, [_vp]),
+    ("fcp_host_register", _i, [_vp, _u64, ctypes.POINTER(_vp)]),
+    ("fcp_host_unregister", _i, [_vp]),
+    ("fcp_pack", _i, [_vp, _vp, _i, _vp]),
+    ("fcp_scatter", _i, [_vp, _vp, _i, _vp]),
+    ("fcp_read_checksums", _i, [_vp, _vp, _vp]),
+    ("fcp_launch", _i, [_vp, _u64, _u64, _u32, _u64, _u64, _vp, _vp, _vp, _i, _i, _vp]),
+    ("fcp_finish_checksums", _i, [_vp, _u64, _u64, _u32, _vp]),
+    ("fcp_save_async", _i, [_vp, _vp, _vp, _i, _i, _vp]),
+    ("fcp_save_packed_wait", _i, [_vp]),
+    ("fcp_save_wait", _i, [_vp, _vp]),
+    ("fcp_restore", _i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
+    ("fcp_restore_from_device", _i, [_vp, _vp, _i, _vp, _vp]),
+    ("fcp_plan_timings", _i, [_vp, _vp]),
+    ("fcp_plan_set_slice_bytes", _i, [_vp, _u64]),
+]
+
+_lib = None
+
+
+class FcpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libfcp: %s (%s)" % (msg, errno.errorcode.get(-code, code)))
+        self.code = code
+
+
+class ChecksumMismatch(FcpError):
+    pass
+
+
+def lib():
+    """Load libfcp.so, loudly."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                "%s is missing: build it with `python -m "
+                "dlrover_wuqiong_b200.csrc.build` (there is no CPU fallback "
+                "for the flash-checkpoint GPU path)" % LIB_PATH)
+        l = ctypes.CDLL(LIB_PATH)
+        for name, res, args in SYMBOLS:
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(rc):
+    if rc == 0:
+        return
+    msg = lib().fcp_last_error().decode("utf-8", "replace")
+    if rc == -errno.EBADMSG:
+        raise ChecksumMismatch(rc, msg)
+    raise FcpError(rc, msg)
+
+
+def make_descs(ptrs, offsets, nbytes):
+    d = np.zeros(len(ptrs), dtype=DESC_DTYPE)
+    d["ptr"] = ptrs
+    d["dst_off"] = offsets
+    d["nbytes"] = nbytes
+    return d
+
+
+class Plan:
+    """Owner of one fcp_plan."""
+
+    def __init__(self, descs, total_bytes, device, chunk_bytes=DEFAULT_CHUNK_BYTES):
+        descs = np.ascontiguousarray(descs, dtype=DESC_DTYPE)
+        self._h = ctypes.c_void_p()
+        check(lib().fcp_plan_create(
+            descs.ctypes.data if len(descs) else None, len(descs), total_bytes,
+            chunk_bytes, device, ctypes.byref(self._h)))
+        self.total_bytes = int(total_bytes)
+        self.chunk_bytes = int(chunk_bytes)
+        self.device = device
+        self.n_desc = len(descs)
+        self.num_chunks = int(lib().fcp_plan_num_chunks(self._h))
+        self.num_regions = int(lib().fcp_plan_num_regions(self._h))
+
+    @property
+    def staging_bytes(self):
+        return max(self.num_regions, 1) * REGION_BYTES
+
+    def update_ptrs(self, ptrs):
+        a = np.ascontiguousarray(ptrs, dtype=np.uint64)
+        check(lib().fcp_plan_update_ptrs(self._h, a.ctypes.data if len(a) else None, len(a)))
+
+    def set_slice_bytes(self, n):
+        check(lib().fcp_plan_set_slice_bytes(self._h, n))
+
+    def pack(self, packed_ptr, checksum=SUM_CRC32C, stream=0):
+        check(lib().fcp_pack(self._h, packed_ptr, checksum, stream))
+
+    def scatter(self, packed_ptr, checksum=SUM_CRC32C, stream=0):
+        check(lib().fcp_scatter(self._h, packed_ptr, checksum, stream))
+
+    def read_checksums(self, stream=0):
+        out = np.zeros(self.num_chunks, dtype=np.uint32)
+        check(lib().fcp_read_checksums(self._h, out.ctypes.data, stream))
+        return out
+
+    def save_async(self, staging_ptr, host_ptr, mode=MODE_STAGED,
+                   checksum=SUM_CRC32C, stream=0):
+        check(lib().fcp_save_async(self._h, staging_ptr, host_ptr, mode, checksum, stream))
+
+    def save_packed_wait(self):
+        check(lib().fcp_save_packed_wait(self._h))
+
+    def save_wait(self, want_sums=True):
+        out = np.zeros(self.num_chunks, dtype=np.uint32) if want_sums else None
+        check(lib().fcp_save_wait(self._h, out.ctypes.data if want_sums else None))
+        return out
+
+    def restore(self, host_ptr, staging_ptr, mode=MODE_STAGED, checksum=SUM_CRC32C,
+                expected=None, stream=0):
+        exp = None
+        if expected is not None:
+            exp = np.ascontiguousarray(expected, dtype=np.uint32)
+            if len(exp) != self.num_chunks:
+                raise ValueError("expected %d checksums, got %d" % (self.num_chunks, len(exp)))
+        check(lib().fcp_restore(self._h, host_ptr, staging_ptr, mode, checksum,
+                                exp.ctypes.data if exp is not None else None, stream))
+
+    def restore_from_device(self, packed_ptr, checksum=SUM_CRC32C, expected=None, stream=0):
+        exp = None
+        if expected is not None:
+            exp = np.ascontiguousarray(expected, dtype=np.uint32)
+        check(lib().fcp_restore_from_device(
+            self._h, packed_ptr, checksum,
+            exp.ctypes.data if exp is not None else None, stream))
+
+    def timings(self):
+        out = (ctypes.c_float * 3)()
+        check(lib().fcp_plan_timings(self._h, out))
+        return {"kernel_ms": out[0], "copy_ms": out[1], "total_ms": out[2]}
+
+    def close(self):
+        if self._h:
+            lib().fcp_plan_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def host_register(addr, nbytes):
+    alias = ctypes.c_void_p()
+    check(lib().fcp_host_register(addr, nbytes, ctypes.byref(alias)))
+    return alias.value
+
+
+def host_unregister(addr):
+    check(lib().fcp_host_unregister(addr))
+
+
+def finish_checksums(raw, total_bytes, chunk_bytes=DEFAULT_CHUNK_BYTES):
+    raw = np.ascontiguousarray(raw, dtype=np.uint32)
+    out = np.zeros_like(raw)
+    check(lib().fcp_finish_checksums(raw.ctypes.data, len(raw), total_bytes,
+                                     chunk_bytes, out.ctypes.data))
+    return out

@@ -1,0 +1,661 @@
+// fcp.cu — host side of libfcp.so: C ABI declared in include/fcp.h.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared
+//        -Xcompiler -fPIC  (see build.py next to this file)
+#include <errno.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <vector>
+
+#include "fcp_crc.h"
+#include "fcp_kernels2.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define FCP_CUDA(expr)                                                    \
+  do {                                                                    \
+    cudaError_t e_ = (expr);                                              \
+    if (e_ != cudaSuccess)                                                \
+      return fail(-EIO, "%s failed: %s (%s:%d)", #expr,                   \
+                  cudaGetErrorString(e_), __FILE__, __LINE__);            \
+  } while (0)
+
+constexpr int kMaxDevices = 64;
+std::mutex g_init_mu;
+bool g_tab_ready[kMaxDevices] = {false};
+int g_sm_count[kMaxDevices] = {0};
+bool g_attr_done[kMaxDevices] = {false};
+
+inline uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+// RAII device switch
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) ok = false;
+    if (ok && prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+int current_device(int* dev) {
+  FCP_CUDA(cudaGetDevice(dev));
+  if (*dev < 0 || *dev >= kMaxDevices)
+    return fail(-EINVAL, "device index %d out of range", *dev);
+  return 0;
+}
+
+int init_device(int dev) {
+  std::lock_guard<std::mutex> lk(g_init_mu);
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(-EINVAL, "device index %d out of range", dev);
+  if (g_tab_ready[dev]) return 0;
+  DeviceGuard g(dev);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", dev);
+  std::vector<uint32_t> tab(fcpk::kTabWords);
+  fcpcrc::make_table(fcpcrc::shift_bytes(4), &tab[fcpk::kTabT]);
+  fcpcrc::make_table(fcpcrc::shift_bytes(fcpk::kRowBytes - 16), &tab[fcpk::kTabK]);
+  for (int k = 0; k < 5; ++k)
+    fcpcrc::make_table(fcpcrc::shift_bytes(16u << k),
+                       &tab[fcpk::kTabC + k * 1024]);
+  fcpcrc::make_table(fcpcrc::shift_bytes(fcpk::kRegion), &tab[fcpk::kTabF]);
+  FCP_CUDA(cudaMemcpyToSymbol(fcpk::g_fcp_tab, tab.data(),
+                              sizeof(uint32_t) * fcpk::kTabWords));
+  int sms = 0;
+  FCP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  g_sm_count[dev] = sms;
+  g_tab_ready[dev] = true;
+  return 0;
+}
+
+// ---- kernel launch -------------------------------------------------------
+constexpr int kBigThreads = 1024;
+constexpr int kSmallThreads = 256;
+constexpr size_t kSmemBig = sizeof(uint32_t) * (1024 * 32 + 1024 + 5120);
+constexpr size_t kSmemSmall = sizeof(uint32_t) * (1024 + 1024 + 5120);
+
+template <bool PACK, bool CRC>
+int launch_dir(const fcpk::Args& a, int dev, cudaStream_t st) {
+  const uint64_t regions = a.region_end - a.region_begin;
+  if (regions == 0) return 0;
+  const int sms = g_sm_count[dev] > 0 ? g_sm_count[dev] : 148;
+  // Big shape: one 1024-thread CTA per SM with the conflict-free (32x
+  // replicated) update table.  Small shape for images too small to give every
+  // warp of the big grid a region: 256-thread CTAs, unreplicated tables.
+  const bool big = CRC && regions >= static_cast<uint64_t>(sms) * 32;
+  if (big) {
+    auto kern = fcpk::fcp_kernel<PACK, CRC, 32, kBigThreads>;
+    if (!g_attr_done[dev]) {
+      FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<true, true, 32, kBigThreads>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBig));
+      FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<false, true, 32, kBigThreads>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBig));
+      g_attr_done[dev] = true;
+    }
+    kern<<<sms, kBigThreads, kSmemBig, st>>>(a);
+  } else {
+    auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads>;
+    const uint64_t want = ceil_div(regions, kSmallThreads / 32);
+    const uint64_t cap = static_cast<uint64_t>(sms) * 8;
+    const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
+    kern<<<grid, kSmallThreads, CRC ? kSmemSmall : 0, st>>>(a);
+  }
+  FCP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_any(const fcpk::Args& a, int direction, int checksum, int dev,
+               cudaStream_t st) {
+  if (direction == 0)
+    return checksum ? launch_dir<true, true>(a, dev, st)
+                    : launch_dir<true, false>(a, dev, st);
+  return checksum ? launch_dir<false, true>(a, dev, st)
+                  : launch_dir<false, false>(a, dev, st);
+}
+
+int launch_finalize(const uint32_t* region_sums, uint32_t* chunk_sums,
+                    uint64_t n_regions, uint32_t regions_per_chunk,
+                    uint64_t chunk_begin, uint64_t chunk_end, cudaStream_t st) {
+  const uint64_t nc = chunk_end - chunk_begin;
+  if (nc == 0) return 0;
+  const unsigned threads = 64;
+  const unsigned grid = static_cast<unsigned>(ceil_div(nc, threads));
+  fcpk::fcp_finalize_kernel<<<grid, threads, 0, st>>>(
+      region_sums, chunk_sums, n_regions, regions_per_chunk, chunk_begin,
+      chunk_end);
+  FCP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int check_geometry(uint64_t total, uint32_t chunk_bytes) {
+  if (chunk_bytes == 0 || chunk_bytes % FCP_REGION_BYTES != 0)
+    return fail(-EINVAL, "chunk_bytes %u is not a multiple of %u", chunk_bytes,
+                FCP_REGION_BYTES);
+  (void)total;
+  return 0;
+}
+
+}  // namespace
+
+// ===================================================================== plan
+struct fcp_plan {
+  int device = 0;
+  uint64_t total = 0;
+  uint32_t chunk_bytes = 0;
+  uint64_t n_desc = 0;
+  uint64_t n_regions = 0;
+  uint64_t n_chunks = 0;
+  uint64_t slice_bytes = 1ull << 30;
+  std::vector<fcp_desc> h_descs;
+  fcp_desc* d_descs = nullptr;
+  uint32_t* d_region_sums = nullptr;
+  uint32_t* d_chunk_sums = nullptr;
+  uint32_t* h_chunk_sums = nullptr;  // pinned
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_begin = nullptr, ev_packed = nullptr, ev_done = nullptr;
+  cudaEvent_t ev_kern_b = nullptr, ev_kern_e = nullptr;
+  std::vector<cudaEvent_t> ev_slice;  // one per slice, created on demand
+  float t_kernel_ms = 0.f, t_copy_ms = 0.f, t_total_ms = 0.f;
+  bool last_has_sums = false;
+  bool save_in_flight = false;
+  int save_mode = 0;
+};
+
+namespace {
+
+int plan_upload(fcp_plan* p) {
+  if (p->n_desc == 0) return 0;
+  FCP_CUDA(cudaMemcpy(p->d_descs, p->h_descs.data(),
+                      sizeof(fcp_desc) * p->n_desc, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int plan_slice_events(fcp_plan* p, size_t n) {
+  while (p->ev_slice.size() < n) {
+    cudaEvent_t e;
+    FCP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    p->ev_slice.push_back(e);
+  }
+  return 0;
+}
+
+fcpk::Args plan_args(const fcp_plan* p, void* packed, uint64_t rb, uint64_t re) {
+  fcpk::Args a;
+  a.descs = p->d_descs;
+  a.n_desc = static_cast<uint32_t>(p->n_desc);
+  a.total = p->total;
+  a.region_begin = rb;
+  a.region_end = re;
+  a.packed = static_cast<uint8_t*>(packed);
+  a.region_sums = p->d_region_sums;
+  return a;
+}
+
+// kernels for chunks [cb, ce) of the plan, on stream st
+int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
+                uint64_t cb, uint64_t ce, cudaStream_t st) {
+  const uint32_t rpc = p->chunk_bytes / FCP_REGION_BYTES;
+  uint64_t rb = cb * rpc, re = ce * rpc;
+  if (re > p->n_regions) re = p->n_regions;
+  int rc = launch_any(plan_args(p, packed, rb, re), direction, checksum,
+                      p->device, st);
+  if (rc) return rc;
+  if (checksum)
+    rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions, rpc,
+                         cb, ce, st);
+  return rc;
+}
+
+int finish_sums(const uint32_t* raw, uint64_t n_chunks, uint64_t total,
+                uint32_t chunk_bytes, uint32_t* out) {
+  if (n_chunks == 0) return 0;
+  // full chunks: std = raw ^ shift_len(~0) ^ ~0
+  const uint32_t full_c =
+      fcpcrc::apply(fcpcrc::shift_bytes(chunk_bytes), 0xFFFFFFFFu) ^ 0xFFFFFFFFu;
+  for (uint64_t c = 0; c + 1 < n_chunks; ++c) out[c] = raw[c] ^ full_c;
+  // last chunk: the device value is the raw CRC of the data followed by zero
+  // padding up to a whole region; strip the padding first.
+  const uint64_t last_len = total - (n_chunks - 1) * chunk_bytes;
+  const uint64_t padded = ceil_div(last_len, FCP_REGION_BYTES) * FCP_REGION_BYTES;
+  uint32_t v = raw[n_chunks - 1];
+  if (padded != last_len)
+    v = fcpcrc::apply(fcpcrc::unshift_bytes(padded - last_len), v);
+  out[n_chunks - 1] =
+      v ^ fcpcrc::apply(fcpcrc::shift_bytes(last_len), 0xFFFFFFFFu) ^ 0xFFFFFFFFu;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fcp_version(void) { return FCP_VERSION; }
+const char* fcp_last_error(void) { return g_err; }
+int fcp_init(int device) { return init_device(device); }
+
+int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
+                    uint32_t chunk_bytes, int device, fcp_plan** out) {
+  if (!out) return fail(-EINVAL, "out is NULL");
+  *out = nullptr;
+  int rc = check_geometry(total_bytes, chunk_bytes);
+  if (rc) return rc;
+  if (n > 0xFFFFFFF0ull) return fail(-EINVAL, "too many descriptors");
+  uint64_t prev_end = 0;
+  for (uint64_t i = 0; i < n; ++i) {
+    if (descs[i].nbytes == 0)
+      return fail(-EINVAL, "descriptor %llu is empty", (unsigned long long)i);
+    if (descs[i].dst_off < prev_end)
+      return fail(-EINVAL, "descriptor %llu overlaps or is out of order",
+                  (unsigned long long)i);
+    prev_end = descs[i].dst_off + descs[i].nbytes;
+    if (prev_end > total_bytes)
+      return fail(-EINVAL, "descriptor %llu ends beyond total_bytes",
+                  (unsigned long long)i);
+  }
+  rc = init_device(device);
+  if (rc) return rc;
+  DeviceGuard g(device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", device);
+  fcp_plan* p = new fcp_plan();
+  p->device = device;
+  p->total = total_bytes;
+  p->chunk_bytes = chunk_bytes;
+  p->n_desc = n;
+  p->n_regions = ceil_div(total_bytes, FCP_REGION_BYTES);
+  p->n_chunks = ceil_div(total_bytes, chunk_bytes);
+  p->h_descs.assign(descs, descs + n);
+  auto bail = [&](int code) {
+    fcp_plan_destroy(p);
+    return code;
+  };
+#define FCP_TRY(expr)                                                       \
+  do {                                                                      \
+    cudaError_t e_ = (expr);                                                \
+    if (e_ != cudaSuccess)                                                  \
+      return bail(fail(-ENOMEM, "%s failed: %s", #expr, cudaGetErrorString(e_))); \
+  } while (0)
+  FCP_TRY(cudaMalloc(&p->d_descs, sizeof(fcp_desc) * (n ? n : 1)));
+  FCP_TRY(cudaMalloc(&p->d_region_sums,
+                     sizeof(uint32_t) * (p->n_regions ? p->n_regions : 1)));
+  FCP_TRY(cudaMalloc(&p->d_chunk_sums,
+                     sizeof(uint32_t) * (p->n_chunks ? p->n_chunks : 1)));
+  FCP_TRY(cudaMallocHost(&p->h_chunk_sums,
+                         sizeof(uint32_t) * (p->n_chunks ? p->n_chunks : 1)));
+  FCP_TRY(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
+  FCP_TRY(cudaEventCreate(&p->ev_begin));
+  FCP_TRY(cudaEventCreate(&p->ev_packed));
+  FCP_TRY(cudaEventCreate(&p->ev_done));
+  FCP_TRY(cudaEventCreate(&p->ev_kern_b));
+  FCP_TRY(cudaEventCreate(&p->ev_kern_e));
+#undef FCP_TRY
+  rc = plan_upload(p);
+  if (rc) return bail(rc);
+  *out = p;
+  return 0;
+}
+
+int fcp_plan_update_ptrs(fcp_plan* p, const void* const* ptrs, uint64_t n) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (n != p->n_desc)
+    return fail(-EINVAL, "expected %llu pointers, got %llu",
+                (unsigned long long)p->n_desc, (unsigned long long)n);
+  bool changed = false;
+  for (uint64_t i = 0; i < n; ++i)
+    if (p->h_descs[i].ptr != ptrs[i]) {
+      p->h_descs[i].ptr = ptrs[i];
+      changed = true;
+    }
+  if (!changed) return 0;
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  return plan_upload(p);
+}
+
+void fcp_plan_destroy(fcp_plan* p) {
+  if (!p) return;
+  DeviceGuard g(p->device);
+  if (p->copy_stream) cudaStreamSynchronize(p->copy_stream);
+  if (p->d_descs) cudaFree(p->d_descs);
+  if (p->d_region_sums) cudaFree(p->d_region_sums);
+  if (p->d_chunk_sums) cudaFree(p->d_chunk_sums);
+  if (p->h_chunk_sums) cudaFreeHost(p->h_chunk_sums);
+  if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
+  cudaEvent_t evs[] = {p->ev_begin, p->ev_packed, p->ev_done, p->ev_kern_b,
+                       p->ev_kern_e};
+  for (cudaEvent_t e : evs)
+    if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : p->ev_slice) cudaEventDestroy(e);
+  delete p;
+}
+
+uint64_t fcp_plan_total_bytes(const fcp_plan* p) { return p ? p->total : 0; }
+uint64_t fcp_plan_num_chunks(const fcp_plan* p) { return p ? p->n_chunks : 0; }
+uint64_t fcp_plan_num_regions(const fcp_plan* p) { return p ? p->n_regions : 0; }
+
+int fcp_plan_set_slice_bytes(fcp_plan* p, uint64_t slice_bytes) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (slice_bytes == 0 || slice_bytes % p->chunk_bytes != 0)
+    return fail(-EINVAL, "slice_bytes must be a positive multiple of chunk_bytes");
+  p->slice_bytes = slice_bytes;
+  return 0;
+}
+
+int fcp_host_register(void* base, uint64_t bytes, void** dev_alias) {
+  if (!base || bytes == 0) return fail(-EINVAL, "empty host range");
+  cudaError_t e = cudaHostRegister(
+      base, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(-ENOMEM, "cudaHostRegister(%p, %llu) failed: %s", base,
+                (unsigned long long)bytes, cudaGetErrorString(e));
+  }
+  if (dev_alias) {
+    void* d = nullptr;
+    e = cudaHostGetDevicePointer(&d, base, 0);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      cudaHostUnregister(base);
+      return fail(-EIO, "cudaHostGetDevicePointer failed: %s",
+                  cudaGetErrorString(e));
+    }
+    *dev_alias = d;
+  }
+  return 0;
+}
+
+int fcp_host_unregister(void* base) {
+  cudaError_t e = cudaHostUnregister(base);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(-EIO, "cudaHostUnregister failed: %s", cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+}  // extern "C"
+
+// ============================================= kernels-only entry points
+extern "C" {
+
+int fcp_launch(const fcp_desc* descs_dev, uint64_t n, uint64_t total_bytes,
+               uint32_t chunk_bytes, uint64_t region_begin, uint64_t region_end,
+               void* packed, uint32_t* region_sums, uint32_t* chunk_sums,
+               int direction, int checksum, void* stream) {
+  int rc = check_geometry(total_bytes, chunk_bytes);
+  if (rc) return rc;
+  const uint32_t rpc = chunk_bytes / FCP_REGION_BYTES;
+  const uint64_t n_regions = ceil_div(total_bytes, FCP_REGION_BYTES);
+  if (region_begin > region_end || region_end > n_regions)
+    return fail(-EINVAL, "bad region range");
+  if (region_begin % rpc != 0 || (region_end % rpc != 0 && region_end != n_regions))
+    return fail(-EINVAL, "region range is not a whole number of chunks");
+  if (checksum && (!region_sums || !chunk_sums))
+    return fail(-EINVAL, "checksum requested without sum buffers");
+  if (direction != 0 && direction != 1) return fail(-EINVAL, "bad direction");
+  int dev = 0;
+  rc = current_device(&dev);
+  if (rc) return rc;
+  rc = init_device(dev);
+  if (rc) return rc;
+  fcpk::Args a;
+  a.descs = descs_dev;
+  a.n_desc = static_cast<uint32_t>(n);
+  a.total = total_bytes;
+  a.region_begin = region_begin;
+  a.region_end = region_end;
+  a.packed = static_cast<uint8_t*>(packed);
+  a.region_sums = region_sums;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  rc = launch_any(a, direction, checksum, dev, st);
+  if (rc) return rc;
+  if (checksum)
+    rc = launch_finalize(region_sums, chunk_sums, n_regions, rpc,
+                         region_begin / rpc, ceil_div(region_end, rpc), st);
+  return rc;
+}
+
+int fcp_finish_checksums(const uint32_t* raw, uint64_t n_chunks,
+                         uint64_t total_bytes, uint32_t chunk_bytes,
+                         uint32_t* out) {
+  int rc = check_geometry(total_bytes, chunk_bytes);
+  if (rc) return rc;
+  if (n_chunks != ceil_div(total_bytes, chunk_bytes))
+    return fail(-EINVAL, "n_chunks does not match total_bytes/chunk_bytes");
+  return finish_sums(raw, n_chunks, total_bytes, chunk_bytes, out);
+}
+
+static int plan_kernels_only(fcp_plan* p, void* packed, int direction,
+                             int checksum, void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (!packed && p->total) return fail(-EINVAL, "packed is NULL");
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FCP_CUDA(cudaEventRecord(p->ev_kern_b, st));
+  int rc = plan_launch(p, packed, direction, checksum, 0, p->n_chunks, st);
+  if (rc) return rc;
+  FCP_CUDA(cudaEventRecord(p->ev_kern_e, st));
+  p->last_has_sums = checksum != 0;
+  return 0;
+}
+
+int fcp_pack(fcp_plan* p, void* packed, int checksum, void* stream) {
+  return plan_kernels_only(p, packed, 0, checksum, stream);
+}
+
+int fcp_scatter(fcp_plan* p, const void* packed, int checksum, void* stream) {
+  return plan_kernels_only(p, const_cast<void*>(packed), 1, checksum, stream);
+}
+
+int fcp_read_checksums(fcp_plan* p, uint32_t* out, void* stream) {
+  if (!p || !out) return fail(-EINVAL, "NULL argument");
+  if (!p->last_has_sums) return fail(-ENODATA, "last launch had no checksum");
+  DeviceGuard g(p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                           sizeof(uint32_t) * p->n_chunks,
+                           cudaMemcpyDeviceToHost, st));
+  FCP_CUDA(cudaStreamSynchronize(st));
+  return finish_sums(p->h_chunk_sums, p->n_chunks, p->total, p->chunk_bytes, out);
+}
+
+// ======================================================== transfer engine
+int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
+                   int checksum, void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is already in flight");
+  if (!host_dst && p->total) return fail(-EINVAL, "host_dst is NULL");
+  if (mode == FCP_MODE_STAGED && !staging && p->total)
+    return fail(-EINVAL, "staged mode needs a staging buffer");
+  if (mode != FCP_MODE_STAGED && mode != FCP_MODE_DIRECT)
+    return fail(-EINVAL, "bad mode %d", mode);
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  int rc = 0;
+  if (mode == FCP_MODE_DIRECT) {
+    void* alias = nullptr;
+    FCP_CUDA(cudaHostGetDevicePointer(&alias, host_dst, 0));
+    rc = plan_launch(p, alias, 0, checksum, 0, p->n_chunks, st);
+    if (rc) return rc;
+    FCP_CUDA(cudaEventRecord(p->ev_packed, st));
+    FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_packed, 0));
+  } else {
+    const uint64_t cps = p->slice_bytes / p->chunk_bytes;  // chunks per slice
+    const uint64_t n_slices = p->n_chunks ? ceil_div(p->n_chunks, cps) : 0;
+    rc = plan_slice_events(p, n_slices);
+    if (rc) return rc;
+    for (uint64_t s = 0; s < n_slices; ++s) {
+      const uint64_t cb = s * cps;
+      const uint64_t ce = (cb + cps < p->n_chunks) ? cb + cps : p->n_chunks;
+      rc = plan_launch(p, staging, 0, checksum, cb, ce, st);
+      if (rc) return rc;
+      FCP_CUDA(cudaEventRecord(p->ev_slice[s], st));
+      const uint64_t b0 = cb * p->chunk_bytes;
+      uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
+      if (b1 > p->total) b1 = p->total;
+      FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_slice[s], 0));
+      FCP_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(host_dst) + b0,
+                               static_cast<uint8_t*>(staging) + b0, b1 - b0,
+                               cudaMemcpyDeviceToHost, p->copy_stream));
+    }
+    FCP_CUDA(cudaEventRecord(p->ev_packed, st));
+    FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_packed, 0));
+  }
+  if (checksum && p->n_chunks)
+    FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                             sizeof(uint32_t) * p->n_chunks,
+                             cudaMemcpyDeviceToHost, p->copy_stream));
+  FCP_CUDA(cudaEventRecord(p->ev_done, p->copy_stream));
+  p->last_has_sums = checksum != 0;
+  p->save_in_flight = true;
+  p->save_mode = mode;
+  return 0;
+}
+
+int fcp_save_packed_wait(fcp_plan* p) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (!p->save_in_flight) return fail(-EINVAL, "no save in flight");
+  FCP_CUDA(cudaEventSynchronize(p->ev_packed));
+  return 0;
+}
+
+int fcp_save_wait(fcp_plan* p, uint32_t* chunk_sums) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (!p->save_in_flight) return fail(-EINVAL, "no save in flight");
+  p->save_in_flight = false;
+  FCP_CUDA(cudaEventSynchronize(p->ev_done));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_kernel_ms, p->ev_begin, p->ev_packed));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
+  p->t_copy_ms = p->t_total_ms - p->t_kernel_ms;
+  if (chunk_sums) {
+    if (!p->last_has_sums) return fail(-ENODATA, "save ran without checksum");
+    return finish_sums(p->h_chunk_sums, p->n_chunks, p->total, p->chunk_bytes,
+                       chunk_sums);
+  }
+  return 0;
+}
+
+static int verify_sums(fcp_plan* p, const uint32_t* expected) {
+  std::vector<uint32_t> got(p->n_chunks);
+  int rc = finish_sums(p->h_chunk_sums, p->n_chunks, p->total, p->chunk_bytes,
+                       got.data());
+  if (rc) return rc;
+  for (uint64_t c = 0; c < p->n_chunks; ++c)
+    if (got[c] != expected[c])
+      return fail(-EBADMSG,
+                  "checksum mismatch in chunk %llu: expected %08x, got %08x",
+                  (unsigned long long)c, expected[c], got[c]);
+  return 0;
+}
+
+int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
+                int checksum, const uint32_t* expected, void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
+  if (!host_src && p->total) return fail(-EINVAL, "host_src is NULL");
+  if (expected && !checksum)
+    return fail(-EINVAL, "expected sums given but checksum disabled");
+  if (mode == FCP_MODE_STAGED && !staging && p->total)
+    return fail(-EINVAL, "staged mode needs a staging buffer");
+  if (mode != FCP_MODE_STAGED && mode != FCP_MODE_DIRECT)
+    return fail(-EINVAL, "bad mode %d", mode);
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = 0;
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  if (mode == FCP_MODE_DIRECT) {
+    void* alias = nullptr;
+    FCP_CUDA(cudaHostGetDevicePointer(&alias, const_cast<void*>(host_src), 0));
+    rc = plan_launch(p, alias, 1, checksum, 0, p->n_chunks, st);
+    if (rc) return rc;
+  } else {
+    // copies start once the caller's stream reaches this point
+    FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_begin, 0));
+    const uint64_t cps = p->slice_bytes / p->chunk_bytes;
+    const uint64_t n_slices = p->n_chunks ? ceil_div(p->n_chunks, cps) : 0;
+    rc = plan_slice_events(p, n_slices);
+    if (rc) return rc;
+    for (uint64_t s = 0; s < n_slices; ++s) {
+      const uint64_t cb = s * cps;
+      const uint64_t ce = (cb + cps < p->n_chunks) ? cb + cps : p->n_chunks;
+      const uint64_t b0 = cb * p->chunk_bytes;
+      uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
+      if (b1 > p->total) b1 = p->total;
+      FCP_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(staging) + b0,
+                               static_cast<const uint8_t*>(host_src) + b0,
+                               b1 - b0, cudaMemcpyHostToDevice, p->copy_stream));
+      FCP_CUDA(cudaEventRecord(p->ev_slice[s], p->copy_stream));
+      FCP_CUDA(cudaStreamWaitEvent(st, p->ev_slice[s], 0));
+      rc = plan_launch(p, staging, 1, checksum, cb, ce, st);
+      if (rc) return rc;
+    }
+  }
+  if (checksum && p->n_chunks)
+    FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                             sizeof(uint32_t) * p->n_chunks,
+                             cudaMemcpyDeviceToHost, st));
+  FCP_CUDA(cudaEventRecord(p->ev_done, st));
+  FCP_CUDA(cudaEventSynchronize(p->ev_done));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
+  p->t_kernel_ms = 0.f;
+  p->t_copy_ms = 0.f;
+  p->last_has_sums = checksum != 0;
+  if (expected) return verify_sums(p, expected);
+  return 0;
+}
+
+int fcp_restore_from_device(fcp_plan* p, const void* packed, int checksum,
+                            const uint32_t* expected, void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (expected && !checksum)
+    return fail(-EINVAL, "expected sums given but checksum disabled");
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  int rc = plan_launch(p, const_cast<void*>(packed), 1, checksum, 0,
+                       p->n_chunks, st);
+  if (rc) return rc;
+  if (checksum && p->n_chunks)
+    FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                             sizeof(uint32_t) * p->n_chunks,
+                             cudaMemcpyDeviceToHost, st));
+  FCP_CUDA(cudaEventRecord(p->ev_done, st));
+  FCP_CUDA(cudaEventSynchronize(p->ev_done));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
+  p->t_kernel_ms = p->t_total_ms;
+  p->t_copy_ms = 0.f;
+  p->last_has_sums = checksum != 0;
+  if (expected) return verify_sums(p, expected);
+  return 0;
+}
+
+int fcp_plan_timings(fcp_plan* p, float* out3) {
+  if (!p || !out3) return fail(-EINVAL, "NULL argument");
+  out3[0] = p->t_kernel_ms;
+  out3[1] = p->t_copy_ms;
+  out3[2] = p->t_total_ms;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,185 @@
+/*
+ * fcp.h — C ABI of the B200 flash-checkpoint data path (libfcp.so).
+ *
+ * The reference (DLRover flash checkpoint) has NO native code on this path:
+ * its "kernel" is a Python loop issuing one pageable torch copy_ per tensor.
+ * Each entry point below therefore names the reference *Python* interface it
+ * replaces (paths relative to the reference tree):
+ *
+ *   SAVER = dlrover/python/elastic_agent/torch/ckpt_saver.py
+ *   FSDPE = dlrover/trainer/torch/flash_checkpoint/fsdp_engine.py
+ *   REPL  = dlrover/trainer/torch/flash_checkpoint/replica.py
+ *
+ * Conventions: plain pointers and sizes, no torch types; every function
+ * returns 0 on success or a negative errno-style code and never throws;
+ * fcp_last_error() returns a thread-local message for the last failure.
+ * All byte movement is asynchronous on the stream passed in unless the
+ * function name ends in _wait or the comment says otherwise.
+ * `stream` arguments are cudaStream_t passed as void* (0 = legacy default).
+ *
+ * Packed image layout (== the reference shm layout, SAVER:255-270): tensor i
+ * occupies bytes [dst_off_i, dst_off_i + nbytes_i) of one dense buffer of
+ * `total_bytes`; offsets are a running byte sum with NO padding, so they are
+ * in general not aligned to anything.  Bytes not covered by any descriptor
+ * are written as zero.
+ *
+ * Checksums (new; the reference has none): standard CRC-32C
+ * (Castagnoli, reflected 0x82F63B78, init/xorout 0xFFFFFFFF) of each window
+ * [i*chunk_bytes, min((i+1)*chunk_bytes, total_bytes)) of the packed image.
+ */
+#ifndef FCP_H_
+#define FCP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FCP_VERSION 1
+
+/* work granularity of the kernels: one warp owns one 16 KiB region (32 rows of
+ * 512 B); chunk_bytes must be a multiple of it.                              */
+#define FCP_REGION_BYTES 16384u
+#define FCP_DEFAULT_CHUNK_BYTES (2u << 20)
+
+/* checksum selector */
+#define FCP_SUM_NONE 0
+#define FCP_SUM_CRC32C 1
+
+/* transfer modes of fcp_save_async / fcp_restore */
+#define FCP_MODE_STAGED 0 /* kernel <-> HBM staging, copy engine <-> host   */
+#define FCP_MODE_DIRECT 1 /* kernel reads/writes host-mapped memory itself  */
+
+/* One tensor of the state dict.  Replaces the (value, TensorMeta) pair that
+ * _write_shared_memory / _read_tensor_from_buf receive (SAVER:197-206,
+ * SAVER:120-137): `ptr` is the tensor's data pointer (device memory, or host
+ * memory that the device can address), `dst_off`/`nbytes` are
+ * TensorMeta.offset and numel*element_size.                                 */
+typedef struct fcp_desc {
+  const void* ptr;
+  uint64_t dst_off;
+  uint64_t nbytes;
+} fcp_desc;
+
+typedef struct fcp_plan fcp_plan;
+
+/* ---- library ----------------------------------------------------------- */
+
+int fcp_version(void);
+const char* fcp_last_error(void);
+/* Upload the CRC tables to `device` (idempotent; done lazily otherwise).    */
+int fcp_init(int device);
+
+/* ---- plan: the descriptor table of one rank's shard -------------------- */
+
+/* Replaces the meta-tree walk of SharedMemoryHandler.save_state_dict
+ * (SAVER:272-290, _traverse_copy_to_shm SAVER:174-194): the caller flattens
+ * the state dict once into `n` descriptors sorted by dst_off, non-overlapping,
+ * nbytes > 0.  The plan owns a device copy of the table plus per-region /
+ * per-chunk checksum buffers, one copy stream and its events.               */
+int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
+                    uint32_t chunk_bytes, int device, fcp_plan** out);
+/* Refresh the tensor pointers only (same layout), e.g. after the optimizer
+ * re-allocated its state; replaces re-walking the dict on later saves
+ * (SAVER:281-282).                                                          */
+int fcp_plan_update_ptrs(fcp_plan* plan, const void* const* ptrs, uint64_t n);
+void fcp_plan_destroy(fcp_plan* plan);
+uint64_t fcp_plan_total_bytes(const fcp_plan* plan);
+uint64_t fcp_plan_num_chunks(const fcp_plan* plan);
+uint64_t fcp_plan_num_regions(const fcp_plan* plan);
+
+/* ---- host memory -------------------------------------------------------- */
+
+/* Pin + map the shm segment that SharedMemoryHandler.init_shared_memory
+ * created (SAVER:313-317, _create_shared_memory SAVER:140-171) so the copy
+ * engines and kernels can address it.  The library never creates or unlinks
+ * the segment.  *dev_alias receives the device-side address of `base`.      */
+int fcp_host_register(void* base, uint64_t bytes, void** dev_alias);
+int fcp_host_unregister(void* base);
+
+/* ---- kernels only (packed image already device-addressable) ------------ */
+
+/* Gather every tensor into the packed image at `packed` (device memory or a
+ * host-mapped alias) with one launch, and — if checksum != FCP_SUM_NONE —
+ * compute the per-chunk CRC32C in the same pass.  Replaces the per-tensor
+ * loop _traverse_copy_to_shm -> _write_shared_memory (SAVER:174-206) and the
+ * FSDP twin _write_memory_from_list -> _write_item (FSDPE:85-155).          */
+int fcp_pack(fcp_plan* plan, void* packed, int checksum, void* stream);
+
+/* Inverse: read the packed image, recompute the per-chunk checksums, and
+ * write every tensor's bytes straight into the live tensor at desc.ptr.
+ * Replaces _read_tensor_from_buf + the caller's per-tensor H2D copy_
+ * (SAVER:120-137, FSDPE:239-297).                                           */
+int fcp_scatter(fcp_plan* plan, const void* packed, int checksum,
+                void* stream);
+
+/* Synchronise `stream` and return the checksums of the last fcp_pack /
+ * fcp_scatter as standard CRC-32C values, one per chunk.                    */
+int fcp_read_checksums(fcp_plan* plan, uint32_t* out, void* stream);
+
+/* Stateless launch used by the two calls above, for callers that own all
+ * memory themselves: `descs_dev` is the descriptor table in device memory,
+ * `region_sums` is scratch of ceil(total_bytes/FCP_REGION_BYTES) uint32,
+ * `chunk_sums` receives one raw (un-finalised) value per chunk; only regions
+ * [region_begin, region_end) — a whole number of chunks — are processed.
+ * direction 0 = pack, 1 = scatter.                                          */
+int fcp_launch(const fcp_desc* descs_dev, uint64_t n, uint64_t total_bytes,
+               uint32_t chunk_bytes, uint64_t region_begin,
+               uint64_t region_end, void* packed, uint32_t* region_sums,
+               uint32_t* chunk_sums, int direction, int checksum,
+               void* stream);
+/* Convert raw per-chunk values produced by fcp_launch into standard CRC-32C
+ * (host-side arithmetic only).                                              */
+int fcp_finish_checksums(const uint32_t* raw, uint64_t n_chunks,
+                         uint64_t total_bytes, uint32_t chunk_bytes,
+                         uint32_t* out);
+
+/* ---- transfer engine ---------------------------------------------------- */
+
+/* Blocking part of SharedMemoryHandler.save_state_dict (SAVER:272-290):
+ * enqueue pack (+checksum) on `stream`, then the device->host transfer into
+ * `host_dst` (registered with fcp_host_register) on the plan's copy stream.
+ * Returns as soon as everything is enqueued.  FCP_MODE_STAGED needs
+ * `staging` = total_bytes rounded up to FCP_REGION_BYTES of device memory
+ * and leaves the live tensors free to change once the pack kernel is done
+ * (fcp_save_packed_wait); FCP_MODE_DIRECT ignores `staging`.                */
+int fcp_save_async(fcp_plan* plan, void* staging, void* host_dst, int mode,
+                   int checksum, void* stream);
+/* Wait until the pack kernel has consumed the live tensors (the training-
+ * blocking part).                                                           */
+int fcp_save_packed_wait(fcp_plan* plan);
+/* Wait until every byte is in host memory; `chunk_sums` (may be NULL)
+ * receives the standard CRC-32C per chunk.                                  */
+int fcp_save_wait(fcp_plan* plan, uint32_t* chunk_sums);
+
+/* SharedMemoryHandler.load_state_dict + the caller's load into the model
+ * (SAVER:292-311 and the per-tensor H2D it implies): move the packed image
+ * from `host_src` into the live tensors, sliced so the host->device copy of
+ * slice k+1 overlaps the scatter of slice k.  If `expected` is non-NULL the
+ * recomputed checksums are compared with it and -EBADMSG is returned on
+ * mismatch (the tensors are then undefined and the caller falls back to
+ * storage, as the reference does when shm holds no valid checkpoint,
+ * SAVER:303-308).  Synchronous: complete on return.                         */
+int fcp_restore(fcp_plan* plan, const void* host_src, void* staging, int mode,
+                int checksum, const uint32_t* expected, void* stream);
+
+/* Peer recovery (replaces the gloo broadcast of shm bytes in
+ * FullCkptReplicaManager.gather, REPL:275-332): the packed image is already
+ * in device memory (received by NCCL broadcast from a surviving replica, or
+ * a peer-mapped pointer); verify and unpack it.  Synchronous.               */
+int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
+                            const uint32_t* expected, void* stream);
+
+/* Device-side milliseconds of the phases of the last save / restore:
+ * out[0] pack or scatter kernels, out[1] host-link copies, out[2] total.    */
+int fcp_plan_timings(fcp_plan* plan, float* out3);
+/* Slice size of the staged pipelines (multiple of chunk_bytes; default
+ * 1 GiB).                                                                   */
+int fcp_plan_set_slice_bytes(fcp_plan* plan, uint64_t slice_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FCP_H_ */
