@@ -1,0 +1,870 @@
+"""Shared-memory data plane and the agent-side asynchronous saver.
+
+Mirror of the reference module dlrover/python/elastic_agent/torch/ckpt_saver.py
+("SAVER" below): same class names, method names, shared-object names and meta
+layout, so engines, checkpointers and third-party saver subclasses written
+against the reference work unchanged.  What changed is *how* bytes move:
+
+* ``SharedMemoryHandler.save_state_dict`` hands every CUDA tensor of the state
+  dict to one pack-kernel launch and a pinned DMA into the shm segment
+  (``transfer.DeviceShardEngine`` -> libfcp.so) instead of one pageable
+  ``copy_`` per tensor (SAVER:174-206);
+* ``SharedMemoryHandler.load_state_dict(into=...)`` scatters the shm image
+  straight into live tensors, verifying the per-chunk CRC-32C recorded at save
+  time; without ``into`` it returns the reference's zero-copy CPU views
+  (SAVER:292-311), which is what the agent-side saver needs.
+
+State dicts that live entirely in host memory (the reference's own CPU tests,
+config 1 of BASELINE.json) never touch CUDA: their bytes are host-to-host
+copies, exactly the reference's path.
+"""
+import importlib
+import os
+import pickle
+import signal
+import threading
+import time
+from abc import ABCMeta, abstractmethod
+from concurrent.futures import ThreadPoolExecutor
+from dataclasses import dataclass
+from enum import Enum, auto
+from pathlib import Path
+from typing import Dict, List, Optional
+
+import torch
+
+from . import plan as _plan
+from .common import env_utils
+from .common.constants import CheckpointConstant, NodeEnv
+from .common.log import default_logger as logger
+from .common.multi_process import SharedDict, SharedLock, SharedMemory, SharedQueue
+from .common.serialize import ClassMeta
+from .plan import TensorMeta  # noqa: F401  (re-exported, reference name)
+
+DLROVER_CKPT_CONFIG_KEY = "_DLORVER_CKPT_CONFIG"
+FCP_CHECKSUM_KEY = "_FCP_CHECKSUMS"
+
+
+class CheckpointSharedObjPrefix:
+    SAVE_STEP_QNAME = "checkpoint_lock_rank_"
+    META_NAME = "checkpoint_meta_"
+    SHM_NAME = "checkpoint_shm_"
+    SHM_LOCK_NAME = "shm_lock_"
+
+
+class CheckpointEventType(Enum):
+    SAVE = auto()
+    UPDATE_SHARD = auto()
+    EXIT = auto()
+
+
+@dataclass
+class CheckpointEvent:
+    type: CheckpointEventType = CheckpointEventType.SAVE
+    step: int = 0
+    global_shard_num: int = 0
+
+
+@dataclass
+class CheckpointConfig:
+    """Per-shard bookkeeping stored in the meta dict under
+    DLROVER_CKPT_CONFIG_KEY (SAVER:73-91).  ``writing_shm`` is True while the
+    shm bytes are being replaced; ``paths`` maps state names to storage paths.
+    """
+    rank: int = 0
+    group_rank: int = 0
+    world_size: int = 0
+    step: int = 0
+    writing_shm: bool = False
+    paths: Dict[str, str] = None  # type: ignore
+
+
+def _traverse_state_dict(value, visitor):
+    return _plan.traverse_state_dict(value, visitor)
+
+
+def _read_tensor_from_buf(value, shm_tensor_buffer):
+    """TensorMeta -> CPU tensor viewing the shm bytes (SAVER:120-137)."""
+    if not isinstance(value, TensorMeta):
+        return value
+    if value.numel == 0:
+        return torch.tensor([], dtype=value.dtype)
+    flat = torch.frombuffer(buffer=shm_tensor_buffer.buf, dtype=value.dtype,
+                            offset=value.offset, count=value.numel)
+    return flat.reshape(value.shape)
+
+
+def _read_state_dict_from_shm(meta_dict, tensor_shm):
+    return _traverse_state_dict(meta_dict, lambda m: _read_tensor_from_buf(m, tensor_shm))
+
+
+def _create_shared_memory(name, create, size=0):
+    """Attach to, or (re)create with exactly `size` bytes, the named segment
+    (SAVER:140-171)."""
+    if not create:
+        try:
+            return SharedMemory(name=name)
+        except FileNotFoundError:
+            return None
+    if size == 0:
+        logger.warning("Cannot create the shared memory with size = 0.")
+        return None
+    try:
+        return SharedMemory(name=name, create=True, size=size)
+    except FileExistsError:
+        shm = SharedMemory(name=name)
+        if shm.size == size:
+            return shm
+        logger.info("shm %s has %d bytes; re-creating it with %d", name, shm.size, size)
+        shm.close()
+        shm.unlink()
+        return SharedMemory(name=name, create=True, size=size)
+
+
+def _host_copy_leaves(leaves, buffer):
+    """Host-resident leaves -> shm, one frombuffer view + copy_ each; this is
+    the reference's own path for CPU tensors (SAVER:197-206)."""
+    for lf in leaves:
+        if lf.nbytes == 0:
+            continue
+        view = torch.frombuffer(buffer, dtype=lf.meta.dtype, count=lf.meta.numel,
+                                offset=lf.meta.offset).reshape(lf.meta.shape)
+        view.copy_(lf.tensor)
+
+
+class PendingSave(object):
+    """Handle of a save whose bytes may still be in flight."""
+
+    def __init__(self, handler, meta_dict, conf, engine):
+        self._handler = handler
+        self._meta = meta_dict
+        self._conf = conf
+        self._engine = engine
+        self._done = False
+
+    def wait_packed(self):
+        """Return once the live tensors may be modified again."""
+        if self._engine is not None and not self._done:
+            self._engine.save_packed_wait()
+
+    def wait(self):
+        """Return once the shm holds the complete shard and the meta says so."""
+        if self._done:
+            return
+        self._done = True
+        h = self._handler
+        if self._engine is not None:
+            sums = self._engine.save_finish()
+            h.last_stats = dict(self._engine.stats)
+            if sums is not None:
+                from .transfer import checksums_to_meta
+                self._meta[FCP_CHECKSUM_KEY] = checksums_to_meta(
+                    sums, self._engine.chunk_bytes)
+            else:
+                self._meta.pop(FCP_CHECKSUM_KEY, None)
+        else:
+            self._meta.pop(FCP_CHECKSUM_KEY, None)
+        self._conf.writing_shm = False
+        h.metadata.set(self._meta)
+
+
+class SharedMemoryHandler(object):
+    """Writes / reads one shard's state dict to / from its shm segment.
+
+    Args:
+        local_rank (int): index of the shard on this node; names the segment
+            ``[<run_id>_]checkpoint_shm_<i>`` and the dict ``checkpoint_meta_<i>``.
+        host (bool): True in the agent (serves the meta dict), False in the
+            training process (client).
+    """
+
+    def __init__(self, local_rank, host=True):
+        self._buffer_size = 0
+        run_id = os.getenv(NodeEnv.TORCHELASTIC_RUN_ID, "")
+        self._shm_name = CheckpointSharedObjPrefix.SHM_NAME + str(local_rank)
+        if run_id:
+            self._shm_name = run_id + "_" + self._shm_name
+        self.shared_memory: Optional[SharedMemory] = None
+        self.metadata = SharedDict(
+            name=CheckpointSharedObjPrefix.META_NAME + str(local_rank), create=host)
+        self._need_creation = True
+        self._engine = None
+        self._n_metas = -1
+        self.last_stats = {}
+
+    # -- lifecycle ----------------------------------------------------------
+    def _drop_engine(self):
+        if self._engine is not None:
+            self._engine.close()  # also drops the pinned mapping of the segment
+            self._engine = None
+
+    def close(self):
+        self._drop_engine()
+        if self.shared_memory:
+            self.shared_memory.close()
+
+    def unlink(self):
+        if not self.shared_memory:
+            # the segment may have been created by another process
+            self.init_shared_memory()
+        if self.shared_memory:
+            self.shared_memory.unlink()
+        if self.metadata:
+            self.metadata.unlink()
+
+    def reset(self):
+        self._need_creation = True
+
+    def init_shared_memory(self, create=False, size=0):
+        self._drop_engine()
+        self.shared_memory = _create_shared_memory(self._shm_name, create=create, size=size)
+        self._need_creation = False
+
+    # -- save -----------------------------------------------------------------
+    def _create_tensor_meta(self, value):
+        """Kept for API parity (SAVER:255-270); the planner does the same walk
+        for the whole dict at once."""
+        if not torch.is_tensor(value):
+            return value
+        meta = TensorMeta(shape=tuple(value.shape), dtype=value.dtype,
+                          element_size=value.element_size(), numel=value.numel(),
+                          offset=self._buffer_size)
+        self._buffer_size += value.numel() * value.element_size()
+        return meta
+
+    def _layout_for(self, state_dict):
+        """(meta_dict, leaves) for this save: the cached layout if the dict
+        still has the same structure, a fresh one (and a fresh segment of the
+        exact size) otherwise."""
+        if self.shared_memory is not None:
+            meta_dict = self.metadata.get(local=True)
+            if meta_dict:
+                leaves = _plan.collect_leaves(state_dict, meta_dict)
+                if leaves is not None and len(leaves) == self._n_metas:
+                    return meta_dict, leaves
+                logger.info("state dict structure changed; rebuilding the shm layout")
+        meta_dict, leaves, total = _plan.build_layout(state_dict)
+        self._buffer_size = total
+        self._n_metas = len(leaves)
+        if self.shared_memory is None or self.shared_memory.size != total:
+            if self.shared_memory is not None:
+                self._drop_engine()
+                self.shared_memory.close()
+            self.init_shared_memory(create=True, size=total)
+        return meta_dict, leaves
+
+    def _engine_for(self, leaves):
+        """The device engine if any leaf with bytes lives on a GPU."""
+        for lf in leaves:
+            if lf.is_cuda and lf.nbytes:
+                dev = lf.tensor.device
+                if self._engine is None or self._engine.device != dev:
+                    self._drop_engine()
+                    from .transfer import DeviceShardEngine
+                    self._engine = DeviceShardEngine(dev)
+                return self._engine
+        return None
+
+    def save_state_dict_async(self, state_dict):
+        meta_dict, leaves = self._layout_for(state_dict)
+        conf = meta_dict.get(DLROVER_CKPT_CONFIG_KEY)
+        if conf is None:
+            conf = CheckpointConfig()
+            meta_dict[DLROVER_CKPT_CONFIG_KEY] = conf
+        conf.writing_shm = True
+        self.metadata.set(meta_dict)
+        engine = self._engine_for(leaves)
+        if self.shared_memory is None:
+            # nothing but empty tensors / scalars: the meta carries it all
+            return PendingSave(self, meta_dict, conf, None)
+        if engine is not None:
+            engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf)
+        else:
+            _host_copy_leaves(leaves, self.shared_memory.buf)
+        return PendingSave(self, meta_dict, conf, engine)
+
+    def save_state_dict(self, state_dict):
+        """Copy the state dict into the shm segment; complete on return
+        (SAVER:272-290)."""
+        self.save_state_dict_async(state_dict).wait()
+
+    # -- load -----------------------------------------------------------------
+    def load_state_dict(self, into=None, device=None):
+        """Without arguments: nested dict of CPU tensors that alias the shm
+        (SAVER:292-311) — consume it before the next save.
+
+        ``into``: a state dict of the same structure whose tensors receive the
+        bytes in place (CUDA tensors through the scatter kernel).  ``device``:
+        allocate fresh tensors there instead.  Both verify the CRC-32C
+        recorded at save time.  Returns {} when the shm holds no complete
+        checkpoint."""
+        meta_dict = self.metadata.get()
+        config = meta_dict.get(DLROVER_CKPT_CONFIG_KEY, CheckpointConfig())
+        if not meta_dict or config.writing_shm:
+            return {}
+        if self.shared_memory is None or self._need_creation:
+            self.init_shared_memory(create=False)
+        if not self.shared_memory:
+            return {}
+        if into is None and device is None:
+            return _read_state_dict_from_shm(_strip_private(meta_dict), self.shared_memory)
+        return self._load_into(meta_dict, into, device)
+
+    def _load_into(self, meta_dict, into, device):
+        total = self.shared_memory.size
+        public = _strip_private(meta_dict)
+        if into is None:
+            dev = torch.device(device)
+
+            def alloc(m):
+                if isinstance(m, TensorMeta):
+                    return torch.empty(m.shape, dtype=m.dtype, device=dev)
+                return m
+
+            into = _traverse_state_dict(public, alloc)
+        leaves = _plan.collect_leaves(into, public, refresh=False)
+        if leaves is None or len(leaves) != _plan.count_tensor_metas(public):
+            raise ValueError("`into` does not match the structure of the checkpoint in memory")
+        engine = self._engine_for(leaves)
+        if engine is not None:
+            from .transfer import checksums_from_meta
+            expected = checksums_from_meta(meta_dict.get(FCP_CHECKSUM_KEY), total,
+                                           engine.chunk_bytes)
+            engine.restore(leaves, total, self.shared_memory.buf, expected)
+            self.last_stats = dict(engine.stats)
+        else:
+            for lf in leaves:
+                if lf.nbytes:
+                    with torch.no_grad():
+                        lf.tensor.copy_(_read_tensor_from_buf(lf.meta, self.shared_memory))
+        it = iter(leaves)
+
+        def fill(m):
+            return next(it).tensor if isinstance(m, TensorMeta) else m
+
+        return _traverse_state_dict(public, fill)
+
+    def restore_from_image(self, meta_dict, image, into):
+        """Unpack a packed image that is not in this handler's shm — e.g. one
+        received from a surviving replica over NCCL — into the tensors of
+        `into`.  `image` is a uint8 tensor (CUDA: scatter kernel with CRC
+        verification; CPU: host copies)."""
+        public = _strip_private(meta_dict)
+        leaves = _plan.collect_leaves(into, public, refresh=False)
+        if leaves is None or len(leaves) != _plan.count_tensor_metas(public):
+            raise ValueError("`into` does not match the structure of the received checkpoint")
+        total = image.numel()
+        if image.is_cuda:
+            engine = self._engine_for(leaves)
+            if engine is None:
+                raise ValueError("device image but no CUDA tensor to restore into")
+            from .transfer import checksums_from_meta
+            expected = checksums_from_meta(meta_dict.get(FCP_CHECKSUM_KEY), total,
+                                           engine.chunk_bytes)
+            engine.restore_from_device(leaves, total, image, expected)
+        else:
+            for lf in leaves:
+                if lf.nbytes:
+                    src = image[lf.meta.offset:lf.meta.offset + lf.nbytes]
+                    with torch.no_grad():
+                        lf.tensor.copy_(src.view(lf.meta.dtype).reshape(lf.meta.shape)
+                                        if lf.meta.offset % lf.meta.element_size == 0
+                                        else src.clone().view(lf.meta.dtype).reshape(lf.meta.shape))
+
+    def no_checkpint_state(self):
+        """True if no shard has ever been saved (handlers attach lazily, so
+        this asks the meta dict, not the segment; SAVER:313-323)."""
+        meta_dict = self.metadata.get()
+        config = meta_dict.get(DLROVER_CKPT_CONFIG_KEY, None)
+        return config is None or config.step == 0
+
+    def get_checkpoint_config(self, default_config):
+        meta_dict = self.metadata.get()
+        return meta_dict.get(DLROVER_CKPT_CONFIG_KEY, default_config)
+
+
+def _strip_private(meta_dict):
+    """The meta dict without the keys this build adds on top of the
+    reference's layout."""
+    if FCP_CHECKSUM_KEY in meta_dict:
+        return {k: v for k, v in meta_dict.items() if k != FCP_CHECKSUM_KEY}
+    return meta_dict
+
+
+# =============================================================== agent side
+class AsyncCheckpointSaver(metaclass=ABCMeta):
+    """Runs in the agent (or a daemon forked by local rank 0): owns the lock,
+    event queue and meta-dict servers of every local shard and persists the
+    shm contents to storage when told to (SAVER:344-770).
+
+    Args:
+        checkpoint_dir (str): root directory of the checkpoints.
+        storage_meta (ClassMeta): how to build the CheckpointStorage.
+        local_shard_num (int): shards (= shm segments) on this node.
+        global_shard_num (int): shards over all nodes.
+        save_timeout (int): seconds to wait for all shards when committing.
+    """
+
+    _saver_instance = None
+    _STAGE_DIR = "._dlrover_ckpt_stage"
+
+    def __init__(self, checkpoint_dir, storage_meta: ClassMeta, local_shard_num=1,
+                 global_shard_num=1, save_timeout=CheckpointConstant.SAVE_TIMEOUT):
+        self.checkpoint_dir = checkpoint_dir
+        self.local_shard_num = local_shard_num
+        self.global_shard_num = global_shard_num
+        self._node_rank = env_utils.get_node_rank()
+        self._is_agent_rank_0 = self._node_rank == 0
+        self._stop_commit = False
+        self._save_timeout = save_timeout
+        storage_cls = getattr(importlib.import_module(storage_meta.module_path),
+                              storage_meta.class_name)
+        self.storage = storage_cls(**storage_meta.kwargs)
+        self._writing_storage = False
+        self._latest_step = 0
+        self._event_queue = SharedQueue(
+            name=CheckpointSharedObjPrefix.SAVE_STEP_QNAME + "0", create=True)
+        self._shm_handlers: List[SharedMemoryHandler] = []
+        self._shm_locks: List[SharedLock] = []
+        for i in range(local_shard_num):
+            self._shm_handlers.append(SharedMemoryHandler(i))
+            self._shm_locks.append(SharedLock(
+                name=CheckpointSharedObjPrefix.SHM_LOCK_NAME + str(i), create=True))
+        self._executor = ThreadPoolExecutor(
+            max_workers=local_shard_num, thread_name_prefix="ckpt_saver-")
+        logger.info("AsyncSaver: checkpoint_dir=%s local_shard_num=%s global_shard_num=%s",
+                    checkpoint_dir, local_shard_num, global_shard_num)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass
+
+    # -- life cycle ----------------------------------------------------------
+    @classmethod
+    def start_async_saving_ckpt(cls):
+        """Start the factory thread: it waits on the queue "factory" for the
+        ClassMeta of the saver the training process wants, builds it and runs
+        its event loop in a second thread (SAVER:409-465)."""
+        factory_queue = SharedQueue(name="factory", create=True)
+        creation_guard = threading.Lock()
+
+        def run_saver(class_meta):
+            if cls._saver_instance is not None:
+                cls._saver_instance.close()
+                cls._saver_instance = None
+            saver_cls = getattr(importlib.import_module(class_meta.module_path),
+                                class_meta.class_name)
+            cls._saver_instance = saver_cls(**class_meta.kwargs)
+            cls._saver_instance._sync_shm_to_storage()
+
+        def factory():
+            logger.info("Start the checkpoint saver factory.")
+            worker = None
+            while True:
+                class_meta = factory_queue.get()
+                with creation_guard:
+                    if cls._saver_instance and worker and worker.is_alive():
+                        logger.info("The saver is already created, skip creating the saver.")
+                        continue
+                    worker = threading.Thread(target=run_saver, args=(class_meta,),
+                                              name="checkpoint-saver", daemon=True)
+                    worker.start()
+
+        threading.Thread(target=factory, name="checkpoint-saver-factory", daemon=True).start()
+
+    @classmethod
+    def get_ckpt_saver(cls):
+        return cls._saver_instance
+
+    @classmethod
+    def register_signal_handler(cls):
+        """SIGINT: drop the shm; SIGTERM: persist it first (SAVER:471-494)."""
+        prev_int = signal.getsignal(signal.SIGINT)
+        prev_term = signal.getsignal(signal.SIGTERM)
+
+        def on_sigint(signum, frame):
+            if cls._saver_instance:
+                cls._saver_instance.close()
+            if callable(prev_int):
+                prev_int(signum, frame)
+
+        def on_sigterm(signum, frame):
+            if cls._saver_instance:
+                cls._saver_instance.save_shm_to_storage()
+                cls._saver_instance.close()
+            if callable(prev_term):
+                prev_term(signum, frame)
+
+        signal.signal(signal.SIGINT, on_sigint)
+        signal.signal(signal.SIGTERM, on_sigterm)
+
+    @classmethod
+    def reset(cls):
+        """Called by the agent when it restarts the workers."""
+        if cls._saver_instance is None:
+            return
+        cls._saver_instance.reset_shared_memory()
+        logger.info("Reset all shared memory of shards.")
+
+    def reset_shared_memory(self):
+        self._stop_commit = True
+        for h in self._shm_handlers:
+            h.reset()
+
+    def wait_saving_checkpoint(self):
+        return self._writing_storage
+
+    def close(self):
+        """Stop the event loop and remove every shared object."""
+        if not self._event_queue.empty():
+            self._event_queue._queue.get()
+        self._event_queue.put(CheckpointEvent(type=CheckpointEventType.EXIT))
+        for i in range(self.local_shard_num):
+            if self._shm_handlers[i]:
+                self._shm_handlers[i].close()
+                self._shm_handlers[i].unlink()
+            self._shm_locks[i].unlink()
+        self._event_queue.unlink()
+        self._executor.shutdown(wait=False)
+
+    def _sync_shm_to_storage(self):
+        """Event loop of the saver thread."""
+        logger.info("Async flash checkpoint saver starts!")
+        while True:
+            event = self._event_queue.get()
+            if event.type == CheckpointEventType.UPDATE_SHARD:
+                logger.info("global shard number is now %s", event.global_shard_num)
+                self.global_shard_num = event.global_shard_num
+            elif event.type == CheckpointEventType.SAVE:
+                logger.info("persist checkpoint, event %s", event)
+                self.save_step_checkpoint(event.step)
+            elif event.type == CheckpointEventType.EXIT:
+                break
+
+    # -- helpers ----------------------------------------------------------------
+    def _shard_config(self, i):
+        return self._shm_handlers[i].get_checkpoint_config(CheckpointConfig())
+
+    def _save_shard(self, step, local_shard_id, ckpt_config, step_done_dir):
+        """Persist one shard under its lock and drop a done-file."""
+        lock = self._shm_locks[local_shard_id]
+        try:
+            handler = self._shm_handlers[local_shard_id]
+            if handler.shared_memory is None:
+                handler.init_shared_memory(create=False)
+            lock.acquire()
+            in_memory = self._shard_config(local_shard_id)
+            if in_memory.step != step:
+                logger.error("event step %s != step %s in memory", step, in_memory.step)
+                return
+            logger.info("persisting shard of rank %s: %s", ckpt_config.rank, ckpt_config)
+            self.persist_to_storage(local_shard_id, ckpt_config)
+            lock.release()
+            self.storage.write("done", os.path.join(step_done_dir, str(ckpt_config.rank)))
+            logger.info("shard of rank %s persisted", ckpt_config.rank)
+            return True
+        except Exception as e:  # noqa: BLE001
+            logger.error("failed to persist shard of rank %s: %s", ckpt_config.rank, e,
+                         exc_info=True)
+            return False
+        finally:
+            lock.release()
+
+    def _dist_make_dir(self, path, timeout=30):
+        if self._node_rank == 0:
+            self.storage.safe_rmtree(path)
+            self.storage.safe_makedirs(path)
+        else:
+            for _ in range(timeout):
+                if self.storage.exists(path):
+                    break
+                time.sleep(1)
+
+    def _any_rank_locked(self):
+        return any(lock.locked() for lock in self._shm_locks)
+
+    def _get_checkpoint_done_dir(self, step):
+        return os.path.join(self.checkpoint_dir, self._STAGE_DIR, str(step) + ".done")
+
+    def _check_shard_step_consistence(self, step, timeout=15):
+        """Poll until every shard that holds a checkpoint holds `step`."""
+        start = time.time()
+        while True:
+            steps = [s for s in (self._shard_config(i).step
+                                 for i in range(self.local_shard_num)) if s > 0]
+            if all(s == step for s in steps):
+                return True
+            time.sleep(1)
+            if time.time() - start > timeout:
+                logger.info("The cached steps are %s", steps)
+                return False
+
+    def _persist_all_shards(self, step, step_done_dir, skip_empty):
+        futures = []
+        for i in range(self.local_shard_num):
+            conf = self._shard_config(i)
+            if skip_empty and conf.step == 0:
+                continue
+            futures.append(self._executor.submit(
+                self._save_shard, step, i, conf, step_done_dir))
+        ok = 0
+        for i, fut in enumerate(futures):
+            if fut.result():
+                ok += 1
+            else:
+                logger.error("failed to persist shard %s of step %s", i, step)
+        return ok == self.local_shard_num
+
+    def save_shm_to_storage(self, timeout=60, master_client=None):
+        """Breakpoint save: persist whatever complete checkpoint the shm holds
+        (agent calls this when workers fail or before restarting them;
+        SAVER:634-693)."""
+        if any(h.no_checkpint_state() for h in self._shm_handlers):
+            logger.info("Skip because no any memory buffer with the state dict.")
+            return
+        steps = [self._shard_config(i).step for i in range(self.local_shard_num)]
+        if len(set(steps)) > 1:
+            logger.error("Skip because steps in shards are inconsistent: %s", steps)
+            return
+        step = steps[0]
+        if master_client and not self._sync_node_checkpoint(master_client, step, timeout):
+            logger.info("Skip saving the checkpoint from the memory to the storage.")
+            self._stop_commit = True
+            return
+        # a held lock means a trainer died mid-copy: the shm may be torn
+        if self._writing_storage or self._any_rank_locked():
+            logger.info("Saver is writing the checkpoint to storage "
+                        "and skips saving at the breakpoint.")
+            return
+        if step > self._latest_step:
+            self.save_step_checkpoint(step)
+            logger.info("Saved the checkpoint of step %s from shm to storage.", step)
+        else:
+            logger.info("The checkpoint of step %s has been saved.", step)
+
+    def _sync_node_checkpoint(self, master_client, step, timeout):
+        """All nodes must agree they can persist `step` (some may have died)."""
+        start = time.time()
+        while True:
+            if master_client.sync_checkpoint(step):
+                return True
+            time.sleep(3)
+            if time.time() - start > timeout:
+                logger.info("timeout syncing the checkpoint step; some nodes may have failed")
+                return False
+
+    @abstractmethod
+    def save_step_checkpoint(self, step: int):
+        """Persist the checkpoint of `step` from shm to storage."""
+
+    @abstractmethod
+    def persist_to_storage(self, local_shard_id, ckpt_config):
+        """Write one shard to the paths in `ckpt_config`."""
+
+    @abstractmethod
+    def commit_checkpoint(self, step: int, step_done_dir: str, timeout=600):
+        """Publish the checkpoint once every shard reported done."""
+
+    @abstractmethod
+    def update_tracker_file(self, step: int):
+        """Record `step` as the latest complete checkpoint."""
+
+
+class CommonDirCheckpointSaver(AsyncCheckpointSaver):
+    """Each shard goes straight to the path its framework chose; the tracker
+    file is updated when the number of done-files equals the number of global
+    shards (SAVER:772-921)."""
+
+    def update_tracker_file(self, step):
+        self.storage.write(str(step), os.path.join(
+            self.checkpoint_dir, CheckpointConstant.TRACER_FILE_NAME))
+
+    def save_step_checkpoint(self, step: int):
+        if not self._check_shard_step_consistence(step):
+            logger.warning("Skip persisting step %s: cached steps are not consistent.", step)
+            return
+        self._writing_storage = True
+        try:
+            step_done_dir = self._get_checkpoint_done_dir(step)
+            self._dist_make_dir(step_done_dir)
+            if not self._persist_all_shards(step, step_done_dir, skip_empty=True):
+                logger.error("node %s failed to save step %s", self._node_rank, step)
+                return
+            self._latest_step = step
+            if self._is_agent_rank_0:
+                self._stop_commit = False
+                self.commit_checkpoint(step, step_done_dir, timeout=self._save_timeout)
+        finally:
+            # (the reference leaves the flag set after a failed save, which
+            # disables every later breakpoint save)
+            self._writing_storage = False
+
+    def commit_checkpoint(self, step: int, step_done_dir: str, timeout=600):
+        start = time.time()
+        success = False
+        while True:
+            if self._stop_commit:
+                logger.info("Stop committing: the training processes restarted.")
+                break
+            done_files = self.storage.listdir(step_done_dir)
+            if len(done_files) == self.global_shard_num:
+                logger.info("All agents finish saving checkpoint for step %s", step)
+                self.update_tracker_file(step)
+                self.storage.safe_rmtree(step_done_dir)
+                success = True
+                break
+            logger.info("ready shards %s != %s", len(done_files), self.global_shard_num)
+            if round(time.time() - start, 2) > timeout:
+                logger.error("commit of step %s timed out; done files: %s", step, done_files)
+                self.storage.safe_rmtree(step_done_dir)
+                break
+            time.sleep(5)
+        self.storage.commit(step, success)
+
+    def persist_to_storage(self, local_shard_id, ckpt_config):
+        state_dict = self._shm_handlers[local_shard_id].load_state_dict()
+        for state_name, sd in state_dict.items():
+            if sd and state_name in ckpt_config.paths:
+                self.storage.write_state_dict(sd, ckpt_config.paths[state_name], torch.save)
+
+
+class TempDirCheckpointSaver(AsyncCheckpointSaver):
+    """Shards are first written below ``<dir>/._dlrover_ckpt_stage/<step>/``
+    and the folder is moved into place when all are done (SAVER:924-1114)."""
+
+    def update_tracker_file(self, step):
+        self.storage.write(str(step), os.path.join(
+            self.checkpoint_dir, CheckpointConstant.TRACER_FILE_NAME))
+
+    def save_step_checkpoint(self, step):
+        logger.info("node %s persists step %s", self._node_rank, step)
+        if not self._check_shard_step_consistence(step):
+            logger.warning("Skip persisting step %s: cached steps are not consistent.", step)
+            return
+        self._writing_storage = True
+        try:
+            temp_dir = self._get_tmp_ckpt_dir(step)
+            self._dist_make_dir(temp_dir)
+            step_done_dir = self._get_checkpoint_done_dir(step)
+            self._dist_make_dir(step_done_dir)
+            futures, ckpt_dir = [], ""
+            for i in range(self.local_shard_num):
+                conf = self._shard_config(i)
+                ckpt_dir = self._replace_path_dir(conf, temp_dir)
+                futures.append(self._executor.submit(
+                    self._save_shard, step, i, conf, step_done_dir))
+            ok = sum(1 for fut in futures if fut.result())
+            if ok != self.local_shard_num:
+                logger.error("node %s failed to save step %s", self._node_rank, step)
+                return
+            if self._is_agent_rank_0:
+                self.commit_checkpoint(step, step_done_dir=step_done_dir, tmp_path=temp_dir,
+                                       target_path=ckpt_dir, timeout=self._save_timeout)
+        finally:
+            self._writing_storage = False
+
+    def _replace_path_dir(self, ckpt_config, temp_dir):
+        """Point the shard's paths into `temp_dir`; returns the directory they
+        pointed to (all paths of a shard must share one)."""
+        ckpt_dir = ""
+        if not ckpt_config.paths:
+            return ckpt_dir
+        staged = {}
+        for name, path in ckpt_config.paths.items():
+            path = str(path)
+            path_dir = os.path.dirname(path)
+            staged[name] = path.replace(path_dir, temp_dir)
+            if not ckpt_dir:
+                ckpt_dir = path_dir
+            elif ckpt_dir != path_dir:
+                raise ValueError("The directories must be same. The latest dir is %s and "
+                                 "the current dir of %s is %s" % (ckpt_dir, name, path_dir))
+        ckpt_config.paths = staged
+        return ckpt_dir
+
+    def _get_tmp_ckpt_dir(self, step):
+        return os.path.join(self.checkpoint_dir, self._STAGE_DIR, str(step))
+
+    def commit_checkpoint(self, step, step_done_dir, tmp_path, target_path,  # type: ignore
+                          timeout=600):
+        logger.info("Start commit checkpoint tmp_path: %s, path: %s", tmp_path, target_path)
+        start = time.time()
+        success = False
+        while True:
+            done_files = self.storage.listdir(step_done_dir)
+            if len(done_files) == self.global_shard_num:
+                logger.info("All agents finish saving checkpoint for step %s", step)
+                if os.path.exists(target_path):
+                    if os.path.isdir(target_path):
+                        self.storage.safe_rmtree(target_path)
+                    else:
+                        self.storage.safe_remove(target_path)
+                self.storage.safe_move(tmp_path, target_path)
+                self.storage.safe_rmtree(step_done_dir)
+                self.update_tracker_file(step)
+                success = True
+                break
+            logger.info("ready shards %s != %s", len(done_files), self.global_shard_num)
+            if time.time() - start > timeout:
+                logger.error("commit of step %s timed out; done files: %s", step, done_files)
+                self.storage.safe_rmtree(tmp_path)
+                self.storage.safe_rmtree(step_done_dir)
+                break
+            time.sleep(5)
+        self.storage.commit(step, success)
+
+    def persist_to_storage(self, local_shard_id, ckpt_config):
+        state_dict = self._shm_handlers[local_shard_id].load_state_dict()
+        for state_name, sd in state_dict.items():
+            if sd and state_name in ckpt_config.paths:
+                self.storage.write_state_dict(sd, ckpt_config.paths[state_name], torch.save)
+
+
+class DdpCheckpointSaver(CommonDirCheckpointSaver):
+    """DDP replicas are identical: only node 0 writes."""
+
+    def persist_to_storage(self, local_shard_id, ckpt_config):
+        if self._node_rank != 0:
+            logger.info("Skip and only rank 0 saves checkpoint in a DDP job.")
+            return
+        super().persist_to_storage(local_shard_id, ckpt_config)
+
+
+class _ExtraTrackerSaver(CommonDirCheckpointSaver):
+    TRACER_FILE = ""
+
+    def update_tracker_file(self, step):
+        super().update_tracker_file(step)
+        self.storage.write(str(step), os.path.join(self.checkpoint_dir, self.TRACER_FILE))
+
+
+class MegatronCheckpointSaver(_ExtraTrackerSaver):
+    TRACER_FILE = "latest_checkpointed_iteration.txt"
+
+
+class DeepSpeedCheckpointSaver(_ExtraTrackerSaver):
+    TRACER_FILE = "latest"
+
+
+class FsdpDcpSaver(CommonDirCheckpointSaver):
+    """FSDP distributed checkpoint: the shm image *is* the ``.distcp`` file, so
+    it is written out raw; node 0 / shard 0 also writes the pickled DCP
+    ``.metadata`` and the tracker (SAVER:1165-1197)."""
+
+    def persist_to_storage(self, local_shard_id, ckpt_config):
+        handler = self._shm_handlers[local_shard_id]
+        path = ckpt_config.paths[CheckpointConstant.MODEL_STATES_NAME]
+        checkpoint_dir = os.path.dirname(path)
+        self._dist_make_dir(checkpoint_dir)
+        assert handler.shared_memory is not None
+        self.storage.write(handler.shared_memory.buf, path)
+        if self._is_agent_rank_0 and local_shard_id == 0:
+            meta_dict = handler.metadata.get()
+            dcp_metadata = meta_dict.get("dcp_metadata", {})
+            if dcp_metadata:
+                self.storage.write(pickle.dumps(dcp_metadata),
+                                   Path(checkpoint_dir) / ".metadata")
+            self.storage.write(str(ckpt_config.step), os.path.join(
+                self.checkpoint_dir, CheckpointConstant.TRACER_FILE_NAME))

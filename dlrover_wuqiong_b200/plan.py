@@ -1,0 +1,122 @@
+"""Shard planner: one walk over a nested state dict produces the reference's
+meta tree (TensorMeta per tensor leaf, dense offsets, SAVER:94-109,255-270 —
+SAVER = dlrover/python/elastic_agent/torch/ckpt_saver.py in the reference) and
+the flat leaf list from which the descriptor table of the CUDA pack / scatter
+kernels is built.
+
+Layout rules kept bit-for-bit: Mapping and list are
+containers, everything else (tuples included) is a leaf; offsets are a running
+sum of numel*element_size with no padding; a tensor reachable twice is laid
+out twice; empty tensors get a meta but no bytes.
+"""
+from collections.abc import Mapping
+from dataclasses import dataclass
+from typing import Tuple
+
+import torch
+
+
+@dataclass
+class TensorMeta:
+    """Same fields as the reference's TensorMeta (SAVER:64-70)."""
+    shape: Tuple[int] = None  # type: ignore
+    dtype: torch.dtype = None  # type: ignore
+    element_size: int = 0
+    numel: int = 0
+    offset: int = 0
+
+
+class Leaf(object):
+    """One tensor leaf in layout order."""
+    __slots__ = ("tensor", "meta", "is_cuda", "nbytes")
+
+    def __init__(self, tensor, meta):
+        self.tensor = tensor
+        self.meta = meta
+        self.is_cuda = tensor.is_cuda
+        self.nbytes = meta.numel * meta.element_size
+
+
+def traverse_state_dict(value, visitor):
+    """Rebuild `value` with every leaf replaced by visitor(leaf)."""
+    if isinstance(value, Mapping):
+        return {k: traverse_state_dict(v, visitor) for k, v in value.items()}
+    if isinstance(value, list):
+        return [traverse_state_dict(v, visitor) for v in value]
+    return visitor(value)
+
+
+def build_layout(state_dict):
+    """-> (meta_tree, leaves, total_bytes).  Non-tensor leaves are carried in
+    the meta tree by value."""
+    leaves = []
+    total = 0
+
+    def visit(v):
+        nonlocal total
+        if not torch.is_tensor(v):
+            return v
+        m = TensorMeta(shape=tuple(v.shape), dtype=v.dtype,
+                       element_size=v.element_size(), numel=v.numel(), offset=total)
+        total += m.numel * m.element_size
+        leaves.append(Leaf(v, m))
+        return m
+
+    meta = traverse_state_dict(state_dict, visit)
+    return meta, leaves, total
+
+
+def collect_leaves(state_dict, meta_tree, refresh=True):
+    """Pair the tensors of `state_dict` with the TensorMeta objects of an
+    existing `meta_tree` of the same structure, refreshing non-tensor leaves in
+    the tree on the way unless refresh=False (what _traverse_copy_to_shm does
+    on later saves, SAVER:174-194).  Returns None if the structure no longer
+    matches."""
+    leaves = []
+
+    def walk(v, m):
+        if isinstance(v, Mapping):
+            if not isinstance(m, dict):
+                return False
+            for k, x in v.items():
+                if isinstance(x, (Mapping, list)) or torch.is_tensor(x):
+                    if k not in m or not walk(x, m[k]):
+                        return False
+                elif refresh:
+                    m[k] = x
+            return True
+        if isinstance(v, list):
+            if not isinstance(m, list) or len(m) != len(v):
+                return False
+            for i, x in enumerate(v):
+                if isinstance(x, (Mapping, list)) or torch.is_tensor(x):
+                    if not walk(x, m[i]):
+                        return False
+                elif refresh:
+                    m[i] = x
+            return True
+        # tensor leaf
+        if not isinstance(m, TensorMeta):
+            return False
+        if (m.numel != v.numel() or m.dtype != v.dtype
+                or tuple(m.shape) != tuple(v.shape)):
+            return False
+        leaves.append(Leaf(v, m))
+        return True
+
+    if not walk(state_dict, meta_tree):
+        return None
+    return leaves
+
+
+def count_tensor_metas(meta_tree):
+    n = 0
+
+    def visit(v):
+        nonlocal n
+        if isinstance(v, TensorMeta):
+            n += 1
+        return v
+
+    traverse_state_dict(meta_tree, visit)
+    return n

@@ -1,0 +1,247 @@
+"""Device side of one rank's shard: owns the native plan (descriptor table on
+the GPU), the HBM staging buffer, the small arena through which host-resident
+leaves join the packed image, and the pinned mapping of the shm segment.
+
+This is the layer that replaces the reference's per-tensor
+``frombuffer(...).copy_(tensor)`` loop (SAVER:197-206) and the per-tensor H2D
+on restore.  There is no CPU fallback here: CUDA tensors in the state dict
+require libfcp.so and a CUDA device, or an exception is raised.
+"""
+import ctypes
+import os
+import time
+
+import numpy as np
+import torch
+
+from . import _native
+from .common.log import default_logger as logger
+
+CHECKSUM_KEY = "_FCP_CHECKSUMS"  # extra top-level meta key (ignored by savers)
+
+
+def _mode_from_env():
+    return _native.MODE_DIRECT if os.getenv("FCP_TRANSFER_MODE", "staged") == "direct" \
+        else _native.MODE_STAGED
+
+
+def buffer_address(buf):
+    """Address of a writable buffer object (mmap / memoryview)."""
+    return ctypes.addressof(ctypes.c_char.from_buffer(buf))
+
+
+class HostMapping(object):
+    """cudaHostRegister'ed view of the shm segment (page-rounded)."""
+
+    def __init__(self, buf, nbytes):
+        self.addr = buffer_address(buf)
+        self.nbytes = nbytes
+        t0 = time.time()
+        _native.host_register(self.addr, nbytes)
+        self.register_s = time.time() - t0
+        self.alive = True
+
+    def close(self):
+        if self.alive:
+            self.alive = False
+            try:
+                _native.host_unregister(self.addr)
+            except Exception as e:  # noqa: BLE001
+                logger.warning("host_unregister failed: %s", e)
+
+
+class DeviceShardEngine(object):
+    """Moves one shard between live tensors and a host buffer."""
+
+    def __init__(self, device, chunk_bytes=_native.DEFAULT_CHUNK_BYTES, checksum=True):
+        if not torch.cuda.is_available():
+            raise RuntimeError(
+                "the state dict holds CUDA tensors but CUDA is not available; "
+                "the flash-checkpoint GPU path has no CPU fallback")
+        _native.lib()  # raises ImportError if the extension is missing
+        self.device = torch.device(device)
+        self.chunk_bytes = chunk_bytes
+        self.checksum = _native.SUM_CRC32C if checksum else _native.SUM_NONE
+        self.mode = _mode_from_env()
+        self._plan = None
+        self._layout_key = None
+        self._staging = None
+        self._arena_dev = None
+        self._arena_pin = None
+        self._mapping = None
+        self._keepalive = []
+        self.stats = {}
+
+    # -- plan -------------------------------------------------------------
+    def _sources(self, leaves):
+        """Device pointers of all non-empty leaves; host leaves are staged
+        through the arena, non-contiguous ones through a temporary."""
+        self._keepalive = []
+        host = [lf for lf in leaves if lf.nbytes and not lf.is_cuda]
+        host_bytes = sum(lf.nbytes for lf in host)
+        if host_bytes:
+            if self._arena_pin is None or self._arena_pin.numel() < host_bytes:
+                self._arena_pin = torch.empty(host_bytes, dtype=torch.uint8).pin_memory()
+                self._arena_dev = torch.empty(host_bytes, dtype=torch.uint8,
+                                              device=self.device)
+        ptrs, offs, sizes, cursor = [], [], [], 0
+        for lf in leaves:
+            if not lf.nbytes:
+                continue
+            t = lf.tensor
+            if lf.is_cuda:
+                if t.device != self.device:
+                    raise RuntimeError("tensor on %s, engine on %s" % (t.device, self.device))
+                if not t.is_contiguous():
+                    t = t.contiguous()  # row-major contents, as copy_ would write
+                    self._keepalive.append(t)
+                ptrs.append(t.data_ptr())
+            else:
+                ptrs.append(self._arena_dev.data_ptr() + cursor)
+                cursor += lf.nbytes
+            offs.append(lf.meta.offset)
+            sizes.append(lf.nbytes)
+        return ptrs, offs, sizes, host
+
+    def _stage_host_leaves(self, host, to_device):
+        """Host leaves <-> arena (pinned), one async copy for all of them."""
+        if not host:
+            return
+        n = sum(lf.nbytes for lf in host)
+        pin = self._arena_pin[:n]
+        if to_device:
+            cursor = 0
+            for lf in host:
+                src = lf.tensor.detach().contiguous().reshape(-1).view(torch.uint8)
+                pin[cursor:cursor + lf.nbytes].copy_(src)
+                cursor += lf.nbytes
+            self._arena_dev[:n].copy_(pin, non_blocking=True)
+        else:
+            pin.copy_(self._arena_dev[:n], non_blocking=False)
+            cursor = 0
+            for lf in host:
+                t = lf.tensor
+                src = pin[cursor:cursor + lf.nbytes].view(t.dtype).reshape(t.shape)
+                with torch.no_grad():
+                    t.copy_(src)
+                cursor += lf.nbytes
+
+    def _ensure_plan(self, ptrs, offs, sizes, total):
+        key = (total, tuple(offs), tuple(sizes))
+        if self._plan is None or self._layout_key != key:
+            if self._plan is not None:
+                self._plan.close()
+            descs = _native.make_descs(ptrs, offs, sizes)
+            self._plan = _native.Plan(descs, total, self.device.index or 0, self.chunk_bytes)
+            self._layout_key = key
+            slice_bytes = int(os.getenv("FCP_SLICE_BYTES", "0"))
+            if slice_bytes:
+                self._plan.set_slice_bytes(slice_bytes)
+        else:
+            self._plan.update_ptrs(ptrs)
+        need = self._plan.staging_bytes
+        if self.mode == _native.MODE_STAGED and (
+                self._staging is None or self._staging.numel() < need):
+            self._staging = None
+            self._staging = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._plan
+
+    def _ensure_mapping(self, buf, total):
+        addr = buffer_address(buf)
+        if self._mapping is not None and (self._mapping.addr != addr
+                                          or self._mapping.nbytes < total):
+            self._mapping.close()
+            self._mapping = None
+        if self._mapping is None and total:
+            self._mapping = HostMapping(buf, total)
+            self.stats["register_s"] = self._mapping.register_s
+        return addr
+
+    # -- save -------------------------------------------------------------
+    def save_begin(self, leaves, total, buf):
+        """Enqueue pack + transfer of the shard into `buf`; returns once the
+        work is enqueued.  Call save_packed_wait() before mutating the tensors
+        and save_finish() for durability + checksums."""
+        with torch.cuda.device(self.device):
+            t0 = time.perf_counter()
+            ptrs, offs, sizes, host = self._sources(leaves)
+            plan = self._ensure_plan(ptrs, offs, sizes, total)
+            addr = self._ensure_mapping(buf, total)
+            stream = torch.cuda.current_stream(self.device)
+            self._stage_host_leaves(host, to_device=True)
+            t1 = time.perf_counter()
+            staging_ptr = self._staging.data_ptr() if self._staging is not None else None
+            plan.save_async(staging_ptr, addr, self.mode, self.checksum, stream.cuda_stream)
+            self.stats["plan_s"] = t1 - t0
+
+    def save_packed_wait(self):
+        self._plan.save_packed_wait()
+
+    def save_finish(self):
+        sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
+        self._keepalive = []
+        self.stats.update(self._plan.timings())
+        return sums
+
+    # -- restore ----------------------------------------------------------
+    def restore(self, leaves, total, buf, expected=None):
+        """Fill the tensors of `leaves` from the packed image in `buf`."""
+        with torch.cuda.device(self.device):
+            for lf in leaves:
+                if lf.is_cuda and lf.nbytes and not lf.tensor.is_contiguous():
+                    raise ValueError("restore target must be contiguous")
+            ptrs, offs, sizes, host = self._sources(leaves)
+            plan = self._ensure_plan(ptrs, offs, sizes, total)
+            addr = self._ensure_mapping(buf, total)
+            stream = torch.cuda.current_stream(self.device)
+            staging_ptr = self._staging.data_ptr() if self._staging is not None else None
+            checksum = self.checksum if expected is not None else _native.SUM_NONE
+            plan.restore(addr, staging_ptr, self.mode, checksum, expected, stream.cuda_stream)
+            self._stage_host_leaves(host, to_device=False)
+            self.stats.update(self._plan.timings())
+
+    def restore_from_device(self, leaves, total, packed, expected=None):
+        """Same, but the packed image is a device uint8 tensor (peer recovery)."""
+        with torch.cuda.device(self.device):
+            ptrs, offs, sizes, host = self._sources(leaves)
+            plan = self._ensure_plan(ptrs, offs, sizes, total)
+            stream = torch.cuda.current_stream(self.device)
+            checksum = self.checksum if expected is not None else _native.SUM_NONE
+            plan.restore_from_device(packed.data_ptr(), checksum, expected,
+                                     stream.cuda_stream)
+            self._stage_host_leaves(host, to_device=False)
+
+    @property
+    def staging(self):
+        return self._staging
+
+    def close(self):
+        try:
+            if torch.cuda.is_available():
+                torch.cuda.synchronize(self.device)
+        except Exception:  # noqa: BLE001
+            pass
+        if self._plan is not None:
+            self._plan.close()
+            self._plan = None
+        if self._mapping is not None:
+            self._mapping.close()
+            self._mapping = None
+        self._staging = None
+        self._arena_dev = None
+        self._arena_pin = None
+
+
+def checksums_to_meta(sums, chunk_bytes):
+    return {"algo": "crc32c", "chunk_bytes": int(chunk_bytes),
+            "sums": np.asarray(sums, dtype=np.uint32).tolist()}
+
+
+def checksums_from_meta(entry, total, chunk_bytes):
+    if not entry or entry.get("algo") != "crc32c" or \
+            entry.get("chunk_bytes") != chunk_bytes:
+        return None
+    sums = np.asarray(entry["sums"], dtype=np.uint32)
+    if len(sums) != (total + chunk_bytes - 1) // chunk_bytes:
+        return None
+    return sums
