@@ -1,0 +1,507 @@
+"""Flash-checkpoint bench: one "step" = one save of a rank's shard from HBM into
+host shared memory (durable, CRC-32C per 2 MiB chunk) + one restore of it back
+into the live tensors (CRC verified).  See DESIGN.md §7 for the definitions.
+
+    python bench.py --gpus 1 --steps 5 --warmup 3
+    torchrun --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...      # the reference's CPU path (oracle port)
+
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import mmap
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+GB = 1e9
+PCIE_GEN5_X16_GBS = 64.0
+
+WORKLOADS = {
+    # nanoGPT shapes, bias=False, block_size 128: fp32 params (tied
+    # wte/lm_head stored twice, as the reference does) + AdamW step/exp_avg/exp_avg_sq
+    "gpt2-xl-1.5B-adamw-fp32": dict(n_layer=48, n_embd=1600, vocab=50304, block=128),
+    "gpt2-small-124M-adamw-fp32": dict(n_layer=12, n_embd=768, vocab=50304, block=128),
+}
+
+
+def gpt2_param_shapes(n_layer, n_embd, vocab, block):
+    e = n_embd
+    shapes = [("transformer.wte.weight", (vocab, e)), ("transformer.wpe.weight", (block, e))]
+    for i in range(n_layer):
+        p = "transformer.h.%d." % i
+        shapes += [(p + "ln_1.weight", (e,)), (p + "attn.c_attn.weight", (3 * e, e)),
+                   (p + "attn.c_proj.weight", (e, e)), (p + "ln_2.weight", (e,)),
+                   (p + "mlp.c_fc.weight", (4 * e, e)), (p + "mlp.c_proj.weight", (e, 4 * e))]
+    shapes += [("transformer.ln_f.weight", (e,)), ("lm_head.weight", (vocab, e))]
+    return shapes
+
+
+def build_state(workload, device, seed, max_bytes=None):
+    """{"model", "optimizer", "step"} as examples/pytorch/nanogpt/train.py:377-394
+    builds it; synthetic random-init values.  `max_bytes` truncates the layer
+    list (used for the bounded CPU-baseline sample)."""
+    cfg = WORKLOADS[workload]
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    shapes = gpt2_param_shapes(**cfg)
+    model, state, used = {}, {}, 0
+    tied = None
+    idx = 0
+    for name, shape in shapes:
+        numel = int(np.prod(shape))
+        if max_bytes is not None and used + numel * 12 > max_bytes and model:
+            break
+        if name == "lm_head.weight" and tied is not None:
+            model[name] = tied  # tied weight: same tensor, laid out twice
+            used += numel * 4
+            continue
+        w = torch.empty(shape, dtype=torch.float32, device=device).normal_(0, 0.02, generator=g)
+        model[name] = w
+        if name == "transformer.wte.weight":
+            tied = w
+        state[idx] = {
+            "step": torch.tensor(float(1000 + idx), device=device),
+            "exp_avg": torch.empty_like(w).normal_(0, 1e-3, generator=g),
+            "exp_avg_sq": torch.empty_like(w).uniform_(0, 1e-6, generator=g),
+        }
+        idx += 1
+        used += numel * 12 + 4
+    optim = {"state": state, "param_groups": [
+        {"lr": 6e-4, "betas": (0.9, 0.95), "eps": 1e-8, "weight_decay": 0.1,
+         "amsgrad": False, "fused": True, "params": list(range(idx))}]}
+    return {"model": model, "optimizer": optim, "step": 1000}
+
+
+def workload_bytes(workload):
+    """Payload bytes of the full state, from the shapes alone."""
+    total = 0
+    for name, shape in gpt2_param_shapes(**WORKLOADS[workload]):
+        n = int(np.prod(shape))
+        total += n * 4 if name == "lm_head.weight" else n * 12 + 4
+    return total
+
+
+def state_bytes(sd):
+    seen = 0
+
+    def walk(v):
+        nonlocal seen
+        if isinstance(v, dict):
+            for x in v.values():
+                walk(x)
+        elif isinstance(v, list):
+            for x in v:
+                walk(x)
+        elif torch.is_tensor(v):
+            seen += v.numel() * v.element_size()
+
+    walk(sd)
+    return seen
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 6:
+                    continue
+                try:
+                    sm.append(float(f[0]))
+                    mx.append(float(f[1]))
+                except ValueError:
+                    continue
+                for n, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            os.unlink(self.path)
+        except Exception:  # noqa: BLE001
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx),
+                       reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def host_info():
+    info = {"cpus": os.cpu_count()}
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemTotal"):
+                info["mem_total_gb"] = round(int(line.split()[1]) / 1e6, 1)
+            if line.startswith("MemAvailable"):
+                info["mem_available_gb"] = round(int(line.split()[1]) / 1e6, 1)
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node")]
+        info["numa_nodes"] = len(nodes)
+    except Exception:  # noqa: BLE001
+        pass
+    return info
+
+
+# --------------------------------------------------------- CPU baseline legs
+def cpu_reference_steps(workload, steps, warmup, sample_bytes):
+    """The reference's CPU path (oracle port, SAVER:174-206 + 112-137) on a
+    bounded prefix of the workload held in host memory: per step one save
+    into a shared mapping + one restore into the tensors.  Returns
+    (GB/s, seconds per step, sample description, threads)."""
+    from oracle import oracle
+    sd = build_state(workload, "cpu", 1234, max_bytes=sample_bytes)
+    meta, total = oracle.layout(sd)
+    mm = mmap.mmap(-1, total, flags=mmap.MAP_SHARED | mmap.MAP_POPULATE)
+    into = oracle.traverse(sd, lambda v: torch.empty_like(v) if torch.is_tensor(v) else v)
+
+    def step():
+        oracle.ref_save_into(sd, meta, mm)
+        oracle.ref_load_from(meta, mm, into)
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    ok = torch.equal(into["model"]["transformer.wte.weight"], sd["model"]["transformer.wte.weight"])
+    assert ok, "CPU baseline round trip failed"
+    n_tensors = len(oracle.flatten(sd)[0])
+    sample = "%s prefix: %d tensors, %.2f GB, save+restore" % (workload, n_tensors, total / GB)
+    del into, sd
+    mm.close()
+    return 2 * total / dt / GB, dt, sample, torch.get_num_threads()
+
+
+# ------------------------------------------------------------------ helpers
+def _dist_max(x, device):
+    if not dist.is_initialized():
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _barrier_sync(device):
+    if dist.is_initialized():
+        dist.barrier()
+    torch.cuda.synchronize(device)
+
+
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_reference_arm(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path
+    (oracle port) on the host cores; rank 0 only."""
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    gbs, dt, sample, threads = cpu_reference_steps(
+        args.workload, args.steps, args.warmup, int(args.cpu_sample_gb * GB))
+    line = {
+        "impl": "reference", "metric": "flash_ckpt_save_plus_restore_GBps", "value": gbs,
+        "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": args.workload, "sample": sample,
+                   "what": "reference CPU path: per-tensor torch copy_ into a shared "
+                           "mapping + per-tensor copy_ back (oracle port of "
+                           "ckpt_saver.py:174-206,112-137)"},
+        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "host": host_info(),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, local_rank, world):
+    from dlrover_wuqiong_b200 import _native
+    from dlrover_wuqiong_b200.ckpt_saver import (
+        DLROVER_CKPT_CONFIG_KEY, FCP_CHECKSUM_KEY, AsyncCheckpointSaver, CheckpointConfig)
+    from dlrover_wuqiong_b200.common.multi_process import clear_sock_dir
+    from dlrover_wuqiong_b200.flash_checkpoint.ddp import DdpCheckpointer, StorageType
+
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    # ---- size guards (a box driven out of memory is a strike)
+    hi = host_info()
+    workload = args.workload
+    B = workload_bytes(workload)
+    avail = hi.get("mem_available_gb", 1e9) * GB
+    need_host = world * B * 1.15 + (2.5 * args.cpu_sample_gb * GB if world == 1 else 0)
+    free_hbm, _ = torch.cuda.mem_get_info(device)
+    note = None
+    if need_host > 0.85 * avail or 2.3 * B > free_hbm:
+        note = "%s does not fit (host %.0f GB avail, HBM %.0f GB free)" % (
+            workload, avail / GB, free_hbm / GB)
+        workload = "gpt2-small-124M-adamw-fp32"
+        B = workload_bytes(workload)
+
+    sd = build_state(workload, device, 1234 + rank)
+    assert state_bytes(sd) == B
+    n_tensors = sum(1 for _ in _iter_tensors(sd))
+
+    ckpt_dir = os.path.join(tempfile.gettempdir(), "fcpbench_%s" % os.environ["TORCHELASTIC_RUN_ID"])
+    if local_rank == 0:
+        os.makedirs(ckpt_dir, exist_ok=True)
+        AsyncCheckpointSaver.start_async_saving_ckpt()
+    ckpt = DdpCheckpointer(ckpt_dir, local_shard_num=world, global_shard_num=world)
+    handler = ckpt._engine._shm_handler
+    path = os.path.join(ckpt_dir, "bench", "rank_%d.pt" % rank)
+
+    def e2e_step(step):
+        ok = ckpt.save_checkpoint(step, sd, path, storage_type=StorageType.MEMORY)
+        assert ok, "save skipped"
+        ckpt.load_checkpoint(into=sd)
+
+    # ---- warm-up through the public API (first save creates + pins the shm)
+    torch.cuda.synchronize(device)
+    t0 = time.perf_counter()
+    ckpt.save_checkpoint(1, sd, path, storage_type=StorageType.MEMORY)
+    first_save_s = time.perf_counter() - t0
+    register_s = handler.last_stats.get("register_s")
+    for w in range(max(args.warmup, 3)):
+        e2e_step(2 + w)
+
+    # ---- parity at full size: sampled chunks of the shm image against the
+    # oracle's CRC-32C, and restored tensors against a snapshot
+    meta = handler.metadata.get(local=True)
+    sums = np.asarray(meta[FCP_CHECKSUM_KEY]["sums"], dtype=np.uint32)
+    chunk = meta[FCP_CHECKSUM_KEY]["chunk_bytes"]
+    parity = {"chunks_checked": 0, "tensors_checked": 0}
+    if rank == 0:
+        from oracle import oracle
+        shm = np.frombuffer(handler.shared_memory.buf, dtype=np.uint8)
+        for c in sorted({0, 1, len(sums) // 3, len(sums) // 2, len(sums) - 2, len(sums) - 1}):
+            if 0 <= c < len(sums):
+                assert oracle.crc32c(shm[c * chunk:(c + 1) * chunk]) == int(sums[c]), \
+                    "chunk %d CRC differs from oracle" % c
+                parity["chunks_checked"] += 1
+        del shm
+    snap_names = ["transformer.wpe.weight", "transformer.ln_f.weight",
+                  "transformer.h.0.attn.c_proj.weight"]
+    snaps = {n: sd["model"][n].clone() for n in snap_names if n in sd["model"]}
+    for n in snaps:
+        sd["model"][n].zero_()
+    sd["optimizer"]["state"][1]["exp_avg"].add_(1.0)
+    ref_avg = None
+    ckpt.load_checkpoint(into=sd)
+    for n, s in snaps.items():
+        assert torch.equal(sd["model"][n], s), "restore mismatch in %s" % n
+        parity["tensors_checked"] += 1
+    del snaps, ref_avg
+
+    # ---- native handles for the device-timed leg
+    eng = handler._engine
+    plan, mode = eng._plan, eng.mode
+    staging_ptr = eng._staging.data_ptr() if eng._staging is not None else None
+    addr = eng._mapping.addr
+    stream = torch.cuda.current_stream(device)
+    K = args.steps
+    cps = (1 << 30) // chunk
+    n_slices = (plan.num_chunks + cps - 1) // cps if mode == _native.MODE_STAGED else 1
+    launches_per_step = 4 * n_slices
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+
+    # ---- leg 1: `value` — C ABI, inputs resident in HBM, device-timed
+    save_ms, pack_ms, restore_ms = [], [], []
+    _barrier_sync(device)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(K):
+        plan.save_async(staging_ptr, addr, mode, _native.SUM_CRC32C, stream.cuda_stream)
+        step_sums = plan.save_wait()
+        t = plan.timings()
+        save_ms.append(t["total_ms"])
+        pack_ms.append(t["kernel_ms"])
+        plan.restore(addr, staging_ptr, mode, _native.SUM_CRC32C, step_sums, stream.cuda_stream)
+        restore_ms.append(plan.timings()["total_ms"])
+    ev1.record(stream)
+    _barrier_sync(device)
+    dev_ms = _dist_max(ev0.elapsed_time(ev1), device)
+
+    # ---- leg 2: `e2e` — DdpCheckpointer.save_checkpoint(MEMORY) + load_checkpoint(into)
+    _barrier_sync(device)
+    t0 = time.perf_counter()
+    for k in range(K):
+        e2e_step(100 + k)
+    torch.cuda.synchronize(device)
+    e2e_s = _dist_max(time.perf_counter() - t0, device)
+    _barrier_sync(device)
+
+    # ---- leg 3: training-blocking time of a save through the Python API
+    block_s = []
+    for k in range(K):
+        wrapped = {"model_states": sd,
+                   DLROVER_CKPT_CONFIG_KEY: CheckpointConfig(step=200 + k, paths={"model_states": path})}
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        pending = handler.save_state_dict_async(wrapped)
+        pending.wait_packed()
+        block_s.append(time.perf_counter() - t0)
+        pending.wait()
+    clocks = sampler.stop() if rank == 0 else None
+
+    save_blocking_s = _dist_max(statistics.median(block_s), device)
+    save_pack_ms = _dist_max(statistics.median(pack_ms), device)
+    save_durable_ms = _dist_max(statistics.median(save_ms), device)
+    restore_med_ms = _dist_max(statistics.median(restore_ms), device)
+
+    ms_per_step = dev_ms / K
+    value = world * 2 * B / (ms_per_step / 1e3) / GB
+    e2e_value = world * 2 * B / (e2e_s / K) / GB
+
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        gbs, dt, sample, threads = cpu_reference_steps(workload, 3, 1, int(args.cpu_sample_gb * GB))
+        cpu_base = {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port",
+                    "sample": sample, "s_per_step": dt}
+
+    if rank == 0:
+        hbm_peak, peak_src = _peaks()
+        achieved = 2 * B / (statistics.mean(pack_ms) / 1e3) / GB
+        line = {
+            "metric": "flash_ckpt_save_plus_restore_GBps", "value": value, "unit": "GB/s",
+            "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {
+                "workload": workload, "shard_bytes_per_rank": B, "tensors_per_rank": n_tensors,
+                "step": "save HBM->shm (durable, CRC32C/2MiB) + restore shm->live tensors (verified)",
+                "transfer_mode": "staged" if mode == _native.MODE_STAGED else "direct",
+                "l2": "inputs (%.1f GB) larger than L2" % (B / GB), "note": note,
+                "host_link_peak_GBps_per_dir": PCIE_GEN5_X16_GBS},
+            "save_blocking_s": save_blocking_s,
+            "save_blocking_device_s": save_pack_ms / 1e3,
+            "save_durable_s": save_durable_ms / 1e3,
+            "restore_s": restore_med_ms / 1e3,
+            "save_GBps_per_rank": B / (save_durable_ms / 1e3) / GB,
+            "restore_GBps_per_rank": B / (restore_med_ms / 1e3) / GB,
+            "host_link_frac": {"save": B / (save_durable_ms / 1e3) / GB / PCIE_GEN5_X16_GBS,
+                               "restore": B / (restore_med_ms / 1e3) / GB / PCIE_GEN5_X16_GBS},
+            "first_save_s": first_save_s, "host_register_s": register_s,
+            "roofline": {"bound": "hbm", "kernel": "fcp_kernel<PACK,CRC,32,1024> (pack + fused CRC32C)",
+                         "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch_set": 2 * B},
+            "cpu_baseline": cpu_base,
+            "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": B,
+                    "d2h_bytes_per_step": B, "s_per_step": e2e_s / K,
+                    "api": "DdpCheckpointer.save_checkpoint(MEMORY) + load_checkpoint(into=)"},
+            "gpu_launches": launches_per_step * K,
+            "clocks": clocks, "parity": parity, "host": hi,
+        }
+        print(json.dumps(line), flush=True)
+
+    ckpt.close()
+    if dist.is_initialized():
+        dist.barrier()
+    if local_rank == 0:
+        saver = AsyncCheckpointSaver.get_ckpt_saver()
+        if saver is not None:
+            saver.close()
+        clear_sock_dir()
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
+def _iter_tensors(v):
+    if isinstance(v, dict):
+        for x in v.values():
+            yield from _iter_tensors(x)
+    elif isinstance(v, list):
+        for x in v:
+            yield from _iter_tensors(x)
+    elif torch.is_tensor(v):
+        yield v
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="gpt2-xl-1.5B-adamw-fp32", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-sample-gb", type=float, default=4.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ["ROLE_NAME"] = "dlrover-trainer"  # the saver is hosted in-process by local rank 0
+    os.environ.setdefault("TORCHELASTIC_RUN_ID",
+                          "fcpbench_%s" % os.environ.get("MASTER_PORT", os.getpid()))
+    os.environ["LOCAL_WORLD_SIZE"] = str(world)
+    os.environ["LOCAL_RANK"] = str(local_rank)
+    os.environ["NODE_NUM"] = "1"
+    os.environ["NODE_RANK"] = "0"
+    os.environ.setdefault("DLROVER_LOG_LEVEL", "WARNING")
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+    run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -180,3 +180,41 @@ def pack_descs(descs, total):
     if len(descs):
         clib().oracle_pack(descs.ctypes.data, len(descs), _addr(out))
     return out
+
+
+# ------------------------------------------- timed CPU baseline (bench.py only)
+def ref_save_into(state_dict, meta, buf):
+    """The reference's save loop on host tensors, statement for statement:
+    per tensor ``torch.frombuffer(buf, dtype, count, offset).reshape(shape)
+    .copy_(t)`` (SAVER:174-206).  `buf` is a writable buffer (mmap)."""
+    def walk(v, m):
+        if isinstance(v, Mapping):
+            for k in v:
+                walk(v[k], m[k])
+        elif isinstance(v, list):
+            for i, x in enumerate(v):
+                walk(x, m[i])
+        elif torch.is_tensor(v) and v.numel():
+            torch.frombuffer(buf, dtype=v.dtype, count=v.numel(),
+                             offset=m.offset).reshape(v.shape).copy_(v)
+
+    walk(state_dict, meta)
+
+
+def ref_load_from(meta, buf, into):
+    """The reference's restore: zero-copy views over the buffer
+    (SAVER:112-137) followed by the caller's per-tensor ``copy_`` into the
+    live tensors (what module/optimizer.load_state_dict do)."""
+    def walk(m, t):
+        if isinstance(m, Mapping):
+            for k in m:
+                walk(m[k], t[k])
+        elif isinstance(m, list):
+            for i, x in enumerate(m):
+                walk(x, t[i])
+        elif isinstance(m, OMeta) and m.numel:
+            view = torch.frombuffer(buf, dtype=m.dtype, count=m.numel,
+                                    offset=m.offset).reshape(m.shape)
+            t.copy_(view)
+
+    walk(meta, into)

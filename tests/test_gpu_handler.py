@@ -1,0 +1,161 @@
+"""GPU parity of the reference-facing API: SharedMemoryHandler / DdpCheckpointer
+with CUDA state dicts must leave exactly the reference's bytes in shm (golden
+vectors + oracle) and restore bit-exact tensors."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+os.environ.setdefault("ROLE_NAME", "dlrover-trainer")
+os.environ.setdefault("TORCHELASTIC_RUN_ID", "fcp_test_%d" % os.getpid())
+
+from dlrover_wuqiong_b200 import _native  # noqa: E402
+from dlrover_wuqiong_b200.ckpt_saver import (  # noqa: E402
+    DLROVER_CKPT_CONFIG_KEY,
+    FCP_CHECKSUM_KEY,
+    AsyncCheckpointSaver,
+    CheckpointConfig,
+    SharedMemoryHandler,
+)
+from dlrover_wuqiong_b200.common.constants import NodeEnv  # noqa: E402
+from dlrover_wuqiong_b200.common.multi_process import clear_sock_dir  # noqa: E402
+from dlrover_wuqiong_b200.flash_checkpoint.ddp import DdpCheckpointer, StorageType  # noqa: E402
+from oracle import oracle  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def _to_dev(sd, keep_cpu=()):
+    def mv(v):
+        return v.cuda() if torch.is_tensor(v) else v
+    out = oracle.traverse(sd, mv)
+    for k in keep_cpu:
+        out[k] = sd[k]
+    return out
+
+
+@pytest.mark.parametrize("name", ["simplenet_sgd_9640", "toymodel_adam_1632", "quirks",
+                                  "mlp_adamw_stepped", "noncontig"])
+def test_handler_cuda_state_dict_matches_reference_bytes(golden, name):
+    case = golden["cases"][name]
+    h = SharedMemoryHandler(41, host=True)
+    try:
+        sd = _to_dev(case["state_dict"])
+        if name == "noncontig":  # keep real strided device views
+            base = case["state_dict"]["t"].t().cuda()
+            sd["col_slice"], sd["row_step"], sd["t"] = base[:, 3:11], base[::3], base.t()
+        sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=5, paths={})
+        h.save_state_dict(sd)
+        assert h.shared_memory.size == case["size"]
+        assert bytes(h.shared_memory.buf[:case["size"]]) == case["shm"]
+        meta = h.metadata.get()
+        sums = meta[FCP_CHECKSUM_KEY]["sums"]
+        want = oracle.chunk_crc32c(np.frombuffer(case["shm"], dtype=np.uint8),
+                                   _native.DEFAULT_CHUNK_BYTES)
+        assert sums == want.tolist()
+        # reference-style load: CPU views with the reference's values
+        out = h.load_state_dict()
+        flat_in, _, _ = oracle.flatten(case["state_dict"])
+        flat_out, _, _ = oracle.flatten({k: v for k, v in out.items()
+                                         if k != DLROVER_CKPT_CONFIG_KEY})
+        for (a, _), (b, _) in zip(flat_in, flat_out):
+            assert oracle.tensor_bytes(a).tobytes() == oracle.tensor_bytes(b).tobytes()
+        # device restore into fresh tensors
+        fresh = h.load_state_dict(device="cuda")
+        flat_f, _, _ = oracle.flatten({k: v for k, v in fresh.items()
+                                       if k != DLROVER_CKPT_CONFIG_KEY})
+        for (a, _), (b, _) in zip(flat_in, flat_f):
+            if a.numel():
+                assert b.is_cuda
+                assert oracle.tensor_bytes(a).tobytes() == oracle.tensor_bytes(b).tobytes()
+        if "second" in case:
+            sd2 = _to_dev(case["second"]["state_dict"])
+            sd2[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=6, paths={})
+            h.save_state_dict(sd2)
+            assert bytes(h.shared_memory.buf[:case["size"]]) == case["second"]["shm"]
+    finally:
+        h.unlink()
+        h.close()
+
+
+def test_mixed_host_and_device_leaves_and_corruption():
+    """CPU-resident leaves (AdamW's default `step`, rng states) ride through
+    the arena; a flipped bit in shm is caught by the CRC on restore."""
+    torch.manual_seed(3)
+    model = nn.Sequential(nn.Linear(301, 257), nn.Linear(257, 33)).cuda()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+    model(torch.randn(8, 301, device="cuda")).sum().backward()
+    opt.step()
+    osd = opt.state_dict()
+    assert not osd["state"][0]["step"].is_cuda  # torch keeps it on the host
+    sd = {"model": model.state_dict(), "optimizer": osd,
+          "rng": [torch.get_rng_state(), torch.cuda.get_rng_state()], "step": 1,
+          DLROVER_CKPT_CONFIG_KEY: CheckpointConfig(step=1, paths={})}
+    _, total, expect = oracle.pack({k: v for k, v in sd.items() if k != DLROVER_CKPT_CONFIG_KEY})
+    h = SharedMemoryHandler(42, host=True)
+    try:
+        h.save_state_dict(sd)
+        assert bytes(h.shared_memory.buf[:total]) == expect.tobytes()
+        into = {"model": {k: torch.zeros_like(v) for k, v in model.state_dict().items()},
+                "optimizer": {"state": {i: {k: torch.zeros_like(v) for k, v in s.items()}
+                                        for i, s in osd["state"].items()},
+                              "param_groups": osd["param_groups"]},
+                "rng": [torch.zeros_like(sd["rng"][0]), torch.zeros_like(sd["rng"][1])],
+                "step": 0}
+        out = h.load_state_dict(into=into)
+        assert out["step"] == 1
+        for k, v in model.state_dict().items():
+            assert torch.equal(into["model"][k], v)
+        for i, s in osd["state"].items():
+            for k, v in s.items():
+                assert torch.equal(into["optimizer"]["state"][i][k], v)
+        assert torch.equal(into["rng"][0], sd["rng"][0])
+        h.shared_memory.buf[total // 3] ^= 0x10
+        with pytest.raises(_native.ChecksumMismatch):
+            h.load_state_dict(into=into)
+    finally:
+        h.unlink()
+        h.close()
+
+
+def test_ddp_checkpointer_gpu_roundtrip_and_async():
+    os.environ[NodeEnv.NODE_NUM] = "1"
+    os.environ[NodeEnv.NODE_RANK] = "0"
+    AsyncCheckpointSaver._saver_instance = None
+    AsyncCheckpointSaver.start_async_saving_ckpt()
+    try:
+        torch.manual_seed(9)
+        model = nn.Sequential(nn.Linear(512, 1024), nn.Linear(1024, 77)).cuda()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-3, fused=True)
+        model(torch.randn(4, 512, device="cuda")).sum().backward()
+        opt.step()
+        with tempfile.TemporaryDirectory() as tmpdir:
+            for async_save in (False, True):
+                ckpt = DdpCheckpointer(tmpdir, async_save=async_save)
+                sd = {"model": model.state_dict(), "optimizer": opt.state_dict(), "step": 10}
+                meta, total, expect = oracle.pack(sd)
+                ref = oracle.unpack(meta, expect)  # snapshot before any mutation
+                assert ckpt.save_checkpoint(10, sd, storage_type=StorageType.MEMORY)
+                if async_save:
+                    # the tensors may change as soon as save returns: the image
+                    # in shm must still be the snapshot
+                    with torch.no_grad():
+                        for p in model.parameters():
+                            p.add_(1.0)
+                    ckpt.wait_latest_checkpoint()
+                shm = ckpt._engine._shm_handler.shared_memory
+                assert bytes(shm.buf[:total]) == expect.tobytes()
+                back = ckpt.load_checkpoint(device="cuda")
+                assert back["step"] == 10
+                for k in sd["model"]:
+                    assert back["model"][k].is_cuda
+                    assert torch.equal(back["model"][k].cpu(), ref["model"][k])
+                ckpt.close()
+    finally:
+        if AsyncCheckpointSaver._saver_instance:
+            AsyncCheckpointSaver._saver_instance.close()
+            AsyncCheckpointSaver._saver_instance = None
+        clear_sock_dir()
