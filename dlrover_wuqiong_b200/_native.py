@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libfcp.so")
 
 REGION_BYTES = 16384
+NOALLOC_MAX_BYTES = 65536 * REGION_BYTES
 DEFAULT_CHUNK_BYTES = 2 << 20
 SUM_NONE, SUM_CRC32C = 0, 1
 MODE_STAGED, MODE_DIRECT = 0, 1
@@ -40,6 +41,7 @@ SYMBOLS = [
     ("fcp_read_checksums", _i, [_vp, _vp, _vp]),
     ("fcp_launch", _i, [_vp, _u64, _u64, _u32, _u64, _u64, _vp, _vp, _vp, _i, _i, _vp]),
     ("fcp_finish_checksums", _i, [_vp, _u64, _u64, _u32, _vp]),
+    ("fcp_launch_noalloc", _i, [_vp, _u64, _u64, _u32, _vp, _vp, _i, _i, _vp]),
     ("fcp_save_async", _i, [_vp, _vp, _vp, _i, _i, _vp]),
     ("fcp_save_packed_wait", _i, [_vp]),
     ("fcp_save_wait", _i, [_vp, _vp]),

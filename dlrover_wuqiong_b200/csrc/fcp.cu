@@ -659,3 +659,76 @@ int fcp_plan_timings(fcp_plan* p, float* out3) {
 }
 
 }  // extern "C"
+
+// ================================================= no-allocation entry point
+// Scratch for fcp_launch_noalloc: one uint32 per 16 KiB region of the image.
+// In host code this name is only a handle for cudaGetSymbolAddress; the
+// kernels receive the device address looked up below.
+static __device__ __align__(256) uint32_t
+    g_fcp_noalloc_region_sums[FCP_NOALLOC_MAX_REGIONS];
+
+namespace {
+uint32_t* g_noalloc_ptr[kMaxDevices] = {nullptr};
+std::mutex g_noalloc_mu;
+
+// once per device, with that device current
+int noalloc_scratch(int dev, uint32_t** out) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_fcp_noalloc_region_sums);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail(-EIO, "cudaGetSymbolAddress(scratch) failed on device %d: %s",
+                  dev, cudaGetErrorString(e));
+    }
+    g_noalloc_ptr[dev] = static_cast<uint32_t*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int fcp_launch_noalloc(const fcp_desc* descs_dev, uint64_t n,
+                                  uint64_t total_bytes, uint32_t chunk_bytes,
+                                  void* packed, uint32_t* chunk_sums,
+                                  int direction, int checksum, void* stream) {
+  int rc = check_geometry(total_bytes, chunk_bytes);
+  if (rc) return rc;
+  if (total_bytes > FCP_NOALLOC_MAX_BYTES)
+    return fail(-E2BIG,
+                "image of %llu bytes exceeds the fixed scratch of "
+                "fcp_launch_noalloc (max %llu bytes); use fcp_launch with "
+                "caller-provided scratch",
+                (unsigned long long)total_bytes,
+                (unsigned long long)FCP_NOALLOC_MAX_BYTES);
+  if (direction != 0 && direction != 1) return fail(-EINVAL, "bad direction");
+  if (checksum && !chunk_sums)
+    return fail(-EINVAL, "checksum requested without chunk_sums");
+  if (!packed && total_bytes) return fail(-EINVAL, "packed is NULL");
+  int dev = 0;
+  rc = current_device(&dev);
+  if (rc) return rc;
+  rc = init_device(dev);
+  if (rc) return rc;
+  uint32_t* scratch = nullptr;
+  rc = noalloc_scratch(dev, &scratch);
+  if (rc) return rc;
+  const uint32_t rpc = chunk_bytes / FCP_REGION_BYTES;
+  const uint64_t n_regions = ceil_div(total_bytes, FCP_REGION_BYTES);
+  fcpk::Args a;
+  a.descs = descs_dev;
+  a.n_desc = static_cast<uint32_t>(n);
+  a.total = total_bytes;
+  a.region_begin = 0;
+  a.region_end = n_regions;
+  a.packed = static_cast<uint8_t*>(packed);
+  a.region_sums = scratch;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  rc = launch_any(a, direction, checksum, dev, st);
+  if (rc) return rc;
+  if (checksum)
+    rc = launch_finalize(scratch, chunk_sums, n_regions, rpc, 0,
+                         ceil_div(n_regions, rpc), st);
+  return rc;
+}

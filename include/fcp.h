@@ -136,6 +136,40 @@ int fcp_finish_checksums(const uint32_t* raw, uint64_t n_chunks,
                          uint64_t total_bytes, uint32_t chunk_bytes,
                          uint32_t* out);
 
+/* Same work as fcp_launch over the WHOLE image, for callers that must not
+ * allocate device memory.  No counterpart in the reference.
+ *
+ * Who needs it: a trainer that has handed all of its HBM to a caching
+ * allocator or runs under a hard per-process memory cap, where a raw
+ * cudaMalloc for the per-region scratch can fail or fragment the pool; and
+ * last-gasp callers such as an out-of-memory or breakpoint handler that wants
+ * the state packed before the process dies and by definition has no memory
+ * left to ask for.  cudaMalloc/cudaFree also synchronise the whole device,
+ * which a caller inside a latency-critical step may not afford.
+ *
+ * The per-region checksum scratch lives in a fixed array inside the library
+ * (FCP_NOALLOC_MAX_REGIONS uint32 = 256 KiB, resident on every GPU that loads
+ * the library until the process exits), so total_bytes may not exceed
+ * FCP_NOALLOC_MAX_BYTES (1 GiB); larger images are rejected with -E2BIG.
+ * The caller passes everything else: `descs_dev` (device memory), `packed`,
+ * and `chunk_sums` (device memory, one raw value per chunk, convert with
+ * fcp_finish_checksums).  This call performs no cudaMalloc/cudaFree and calls
+ * no allocating library routine.
+ *
+ * The first call on each device looks up the device address of the scratch
+ * array (and uploads the CRC tables if no other call has yet); make that
+ * first call before starting any stream capture.  All calls on a device share
+ * the one array: every slot a call reads it has written first, so nothing
+ * needs clearing between calls, but two calls whose kernels overlap on the
+ * GPU (different streams, or different threads) race on it — serialise them.
+ * direction 0 = pack, 1 = scatter.                                          */
+#define FCP_NOALLOC_MAX_REGIONS 65536u
+#define FCP_NOALLOC_MAX_BYTES ((uint64_t)FCP_NOALLOC_MAX_REGIONS * FCP_REGION_BYTES)
+int fcp_launch_noalloc(const fcp_desc* descs_dev, uint64_t n,
+                       uint64_t total_bytes, uint32_t chunk_bytes,
+                       void* packed, uint32_t* chunk_sums, int direction,
+                       int checksum, void* stream);
+
 /* ---- transfer engine ---------------------------------------------------- */
 
 /* Blocking part of SharedMemoryHandler.save_state_dict (SAVER:272-290):
