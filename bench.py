@@ -352,9 +352,7 @@ def run_ours(args, rank, local_rank, world):
     addr = eng._mapping.addr
     stream = torch.cuda.current_stream(device)
     K = args.steps
-    cps = (1 << 30) // chunk
-    n_slices = (plan.num_chunks + cps - 1) // cps if mode == _native.MODE_STAGED else 1
-    launches_per_step = 4 * n_slices
+    launches = 0
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -368,10 +366,12 @@ def run_ours(args, rank, local_rank, world):
     for _ in range(K):
         plan.save_async(staging_ptr, addr, mode, _native.SUM_CRC32C, stream.cuda_stream)
         step_sums = plan.save_wait()
+        launches += plan.last_launches()
         t = plan.timings()
         save_ms.append(t["total_ms"])
         pack_ms.append(t["kernel_ms"])
         plan.restore(addr, staging_ptr, mode, _native.SUM_CRC32C, step_sums, stream.cuda_stream)
+        launches += plan.last_launches()
         restore_ms.append(plan.timings()["total_ms"])
     ev1.record(stream)
     _barrier_sync(device)
@@ -445,7 +445,7 @@ def run_ours(args, rank, local_rank, world):
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": B,
                     "d2h_bytes_per_step": B, "s_per_step": e2e_s / K,
                     "api": "DdpCheckpointer.save_checkpoint(MEMORY) + load_checkpoint(into=)"},
-            "gpu_launches": launches_per_step * K,
+            "gpu_launches": launches,
             "clocks": clocks, "parity": parity, "host": hi,
         }
         print(json.dumps(line), flush=True)

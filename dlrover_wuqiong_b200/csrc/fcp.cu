@@ -6,7 +6,9 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
+#include <utility>
 #include <vector>
 
 #include "fcp_crc.h"
@@ -162,7 +164,8 @@ struct fcp_plan {
   uint64_t n_desc = 0;
   uint64_t n_regions = 0;
   uint64_t n_chunks = 0;
-  uint64_t slice_bytes = 1ull << 30;
+  uint64_t slice_bytes = 256ull << 20;  // smallest slice; they grow x2 up to x16
+  uint64_t last_launches = 0;
   std::vector<fcp_desc> h_descs;
   fcp_desc* d_descs = nullptr;
   uint32_t* d_region_sums = nullptr;
@@ -208,19 +211,51 @@ fcpk::Args plan_args(const fcp_plan* p, void* packed, uint64_t rb, uint64_t re) 
   return a;
 }
 
-// kernels for chunks [cb, ce) of the plan, on stream st
+// kernels for chunks [cb, ce) of the plan, on stream st; `finalize` = also
+// combine the region values of those chunks into chunk values
 int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
-                uint64_t cb, uint64_t ce, cudaStream_t st) {
+                uint64_t cb, uint64_t ce, cudaStream_t st, bool finalize = true) {
   const uint32_t rpc = p->chunk_bytes / FCP_REGION_BYTES;
   uint64_t rb = cb * rpc, re = ce * rpc;
   if (re > p->n_regions) re = p->n_regions;
-  int rc = launch_any(plan_args(p, packed, rb, re), direction, checksum,
-                      p->device, st);
-  if (rc) return rc;
-  if (checksum)
-    rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions, rpc,
-                         cb, ce, st);
-  return rc;
+  if (re > rb) {
+    int rc = launch_any(plan_args(p, packed, rb, re), direction, checksum,
+                        p->device, st);
+    if (rc) return rc;
+    p->last_launches++;
+  }
+  if (checksum && finalize && ce > cb) {
+    int rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
+                             rpc, cb, ce, st);
+    if (rc) return rc;
+    p->last_launches++;
+  }
+  return 0;
+}
+
+// Chunk ranges of the staged pipelines.  Sizes double from slice_bytes up to
+// 16x: a save starts its first DMA after a small pack and keeps the copy
+// engine busy behind ever larger (more efficient) kernels; a restore runs
+// the schedule backwards so only a small scatter trails the last DMA.
+std::vector<std::pair<uint64_t, uint64_t>> make_slices(const fcp_plan* p,
+                                                       bool growing) {
+  std::vector<uint64_t> sizes;
+  const uint64_t cps0 = p->slice_bytes / p->chunk_bytes;
+  uint64_t left = p->n_chunks, cur = cps0 ? cps0 : 1;
+  while (left) {
+    const uint64_t take = cur < left ? cur : left;
+    sizes.push_back(take);
+    left -= take;
+    if (cur < 16 * cps0) cur *= 2;
+  }
+  if (!growing) std::reverse(sizes.begin(), sizes.end());
+  std::vector<std::pair<uint64_t, uint64_t>> out;
+  uint64_t at = 0;
+  for (uint64_t sz : sizes) {
+    out.emplace_back(at, at + sz);
+    at += sz;
+  }
+  return out;
 }
 
 int finish_sums(const uint32_t* raw, uint64_t n_chunks, uint64_t total,
@@ -449,6 +484,7 @@ static int plan_kernels_only(fcp_plan* p, void* packed, int direction,
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   FCP_CUDA(cudaEventRecord(p->ev_kern_b, st));
+  p->last_launches = 0;
   int rc = plan_launch(p, packed, direction, checksum, 0, p->n_chunks, st);
   if (rc) return rc;
   FCP_CUDA(cudaEventRecord(p->ev_kern_e, st));
@@ -491,6 +527,7 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
   int rc = 0;
+  p->last_launches = 0;
   if (mode == FCP_MODE_DIRECT) {
     void* alias = nullptr;
     FCP_CUDA(cudaHostGetDevicePointer(&alias, host_dst, 0));
@@ -499,14 +536,12 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
     FCP_CUDA(cudaEventRecord(p->ev_packed, st));
     FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_packed, 0));
   } else {
-    const uint64_t cps = p->slice_bytes / p->chunk_bytes;  // chunks per slice
-    const uint64_t n_slices = p->n_chunks ? ceil_div(p->n_chunks, cps) : 0;
-    rc = plan_slice_events(p, n_slices);
+    const auto slices = make_slices(p, true);
+    rc = plan_slice_events(p, slices.size());
     if (rc) return rc;
-    for (uint64_t s = 0; s < n_slices; ++s) {
-      const uint64_t cb = s * cps;
-      const uint64_t ce = (cb + cps < p->n_chunks) ? cb + cps : p->n_chunks;
-      rc = plan_launch(p, staging, 0, checksum, cb, ce, st);
+    for (size_t s = 0; s < slices.size(); ++s) {
+      const uint64_t cb = slices[s].first, ce = slices[s].second;
+      rc = plan_launch(p, staging, 0, checksum, cb, ce, st, false);
       if (rc) return rc;
       FCP_CUDA(cudaEventRecord(p->ev_slice[s], st));
       const uint64_t b0 = cb * p->chunk_bytes;
@@ -516,6 +551,12 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
       FCP_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(host_dst) + b0,
                                static_cast<uint8_t*>(staging) + b0, b1 - b0,
                                cudaMemcpyDeviceToHost, p->copy_stream));
+    }
+    if (checksum && p->n_chunks) {
+      rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
+                           p->chunk_bytes / FCP_REGION_BYTES, 0, p->n_chunks, st);
+      if (rc) return rc;
+      p->last_launches++;
     }
     FCP_CUDA(cudaEventRecord(p->ev_packed, st));
     FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_packed, 0));
@@ -582,6 +623,7 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = 0;
+  p->last_launches = 0;
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
   if (mode == FCP_MODE_DIRECT) {
     void* alias = nullptr;
@@ -591,13 +633,11 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
   } else {
     // copies start once the caller's stream reaches this point
     FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_begin, 0));
-    const uint64_t cps = p->slice_bytes / p->chunk_bytes;
-    const uint64_t n_slices = p->n_chunks ? ceil_div(p->n_chunks, cps) : 0;
-    rc = plan_slice_events(p, n_slices);
+    const auto slices = make_slices(p, false);
+    rc = plan_slice_events(p, slices.size());
     if (rc) return rc;
-    for (uint64_t s = 0; s < n_slices; ++s) {
-      const uint64_t cb = s * cps;
-      const uint64_t ce = (cb + cps < p->n_chunks) ? cb + cps : p->n_chunks;
+    for (size_t s = 0; s < slices.size(); ++s) {
+      const uint64_t cb = slices[s].first, ce = slices[s].second;
       const uint64_t b0 = cb * p->chunk_bytes;
       uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
       if (b1 > p->total) b1 = p->total;
@@ -606,8 +646,14 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
                                b1 - b0, cudaMemcpyHostToDevice, p->copy_stream));
       FCP_CUDA(cudaEventRecord(p->ev_slice[s], p->copy_stream));
       FCP_CUDA(cudaStreamWaitEvent(st, p->ev_slice[s], 0));
-      rc = plan_launch(p, staging, 1, checksum, cb, ce, st);
+      rc = plan_launch(p, staging, 1, checksum, cb, ce, st, false);
       if (rc) return rc;
+    }
+    if (checksum && p->n_chunks) {
+      rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
+                           p->chunk_bytes / FCP_REGION_BYTES, 0, p->n_chunks, st);
+      if (rc) return rc;
+      p->last_launches++;
     }
   }
   if (checksum && p->n_chunks)
@@ -633,6 +679,7 @@ int fcp_restore_from_device(fcp_plan* p, const void* packed, int checksum,
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  p->last_launches = 0;
   int rc = plan_launch(p, const_cast<void*>(packed), 1, checksum, 0,
                        p->n_chunks, st);
   if (rc) return rc;
@@ -648,6 +695,10 @@ int fcp_restore_from_device(fcp_plan* p, const void* packed, int checksum,
   p->last_has_sums = checksum != 0;
   if (expected) return verify_sums(p, expected);
   return 0;
+}
+
+uint64_t fcp_plan_last_launches(const fcp_plan* p) {
+  return p ? p->last_launches : 0;
 }
 
 int fcp_plan_timings(fcp_plan* p, float* out3) {

@@ -224,7 +224,17 @@ __global__ void fcp_finalize_kernel(const uint32_t* __restrict__ region_sums,
   if (r1 > n_regions) r1 = n_regions;
   const uint32_t* F = g_fcp_tab + kTabF;
   uint32_t acc = 0;
-  for (uint64_t r = r0; r < r1; ++r) acc = lin4(F, acc) ^ region_sums[r];
+  // region values are independent of acc: fetch them 8 at a time so the
+  // serial Horner chain only waits on (L1-resident) table lookups
+  uint64_t r = r0;
+  for (; r + 8 <= r1; r += 8) {
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __ldg(region_sums + r + k);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc = lin4(F, acc) ^ v[k];
+  }
+  for (; r < r1; ++r) acc = lin4(F, acc) ^ __ldg(region_sums + r);
   chunk_sums[c] = acc;
 }
 

@@ -209,8 +209,11 @@ int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
 /* Device-side milliseconds of the phases of the last save / restore:
  * out[0] pack or scatter kernels, out[1] host-link copies, out[2] total.    */
 int fcp_plan_timings(fcp_plan* plan, float* out3);
-/* Slice size of the staged pipelines (multiple of chunk_bytes; default
- * 1 GiB).                                                                   */
+/* Number of kernels the last fcp_save_async / fcp_restore launched.          */
+uint64_t fcp_plan_last_launches(const fcp_plan* plan);
+/* Smallest slice of the staged pipelines (multiple of chunk_bytes; default
+ * 256 MiB).  Slices double in size up to 16x this value; a save runs the
+ * schedule small-to-large, a restore large-to-small.                        */
 int fcp_plan_set_slice_bytes(fcp_plan* plan, uint64_t slice_bytes);
 
 #ifdef __cplusplus
