@@ -4,6 +4,7 @@
 #include <errno.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -71,9 +72,10 @@ int init_device(int dev) {
   if (!g.ok) return fail(-EIO, "cannot select device %d", dev);
   std::vector<uint32_t> tab(fcpk::kTabWords);
   fcpcrc::make_table(fcpcrc::shift_bytes(4), &tab[fcpk::kTabT]);
-  fcpcrc::make_table(fcpcrc::shift_bytes(fcpk::kRowBytes - 16), &tab[fcpk::kTabK]);
+  fcpcrc::make_table(fcpcrc::shift_bytes(fcpk::kRowBytes - fcpk::kWordBytes),
+                     &tab[fcpk::kTabK]);
   for (int k = 0; k < 5; ++k)
-    fcpcrc::make_table(fcpcrc::shift_bytes(16u << k),
+    fcpcrc::make_table(fcpcrc::shift_bytes(static_cast<uint64_t>(fcpk::kWordBytes) << k),
                        &tab[fcpk::kTabC + k * 1024]);
   fcpcrc::make_table(fcpcrc::shift_bytes(fcpk::kRegion), &tab[fcpk::kTabF]);
   FCP_CUDA(cudaMemcpyToSymbol(fcpk::g_fcp_tab, tab.data(),
@@ -88,18 +90,25 @@ int init_device(int dev) {
 // ---- kernel launch -------------------------------------------------------
 constexpr int kBigThreads = 1024;
 constexpr int kSmallThreads = 256;
-constexpr size_t kSmemBig = sizeof(uint32_t) * (1024 * 32 + 1024 + 5120);
+constexpr size_t kSmemBig = sizeof(uint32_t) * (1024 * 32 + 1024 * 16 + 5120);
 constexpr size_t kSmemSmall = sizeof(uint32_t) * (1024 + 1024 + 5120);
 
 template <bool PACK, bool CRC>
-int launch_dir(const fcpk::Args& a, int dev, cudaStream_t st) {
+int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
+  fcpk::Args a = a_in;
   const uint64_t regions = a.region_end - a.region_begin;
   if (regions == 0) return 0;
   const int sms = g_sm_count[dev] > 0 ? g_sm_count[dev] : 148;
+  // longest run that still leaves every warp of a full grid >= 4 visits
+  uint64_t run = regions / (static_cast<uint64_t>(sms) * 32 * 4);
+  a.run = static_cast<uint32_t>(run < 1 ? 1 : run > fcpk::kMaxRun ? fcpk::kMaxRun : run);
   // Big shape: one 1024-thread CTA per SM with the conflict-free (32x
-  // replicated) update table.  Small shape for images too small to give every
-  // warp of the big grid a region: 256-thread CTAs, unreplicated tables.
-  const bool big = CRC && regions >= static_cast<uint64_t>(sms) * 32;
+  // replicated) update table and a 16x replicated row-shift table (212 KiB of
+  // shared memory).  Small shape for images too small to give every warp of
+  // the big grid a region: 256-thread CTAs, unreplicated tables.
+  static const bool force_big = getenv("FCP_DEBUG_FORCE_BIG") != nullptr;  // tuning aid
+  const uint64_t runs = ceil_div(regions, a.run);
+  const bool big = (CRC || force_big) && runs >= static_cast<uint64_t>(sms) * 32;
   if (big) {
     auto kern = fcpk::fcp_kernel<PACK, CRC, 32, kBigThreads>;
     if (!g_attr_done[dev]) {
@@ -109,12 +118,18 @@ int launch_dir(const fcpk::Args& a, int dev, cudaStream_t st) {
       FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<false, true, 32, kBigThreads>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kSmemBig));
+      FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<true, false, 32, kBigThreads>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBig));
+      FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<false, false, 32, kBigThreads>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBig));
       g_attr_done[dev] = true;
     }
     kern<<<sms, kBigThreads, kSmemBig, st>>>(a);
   } else {
     auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads>;
-    const uint64_t want = ceil_div(regions, kSmallThreads / 32);
+    const uint64_t want = ceil_div(runs, kSmallThreads / 32);
     const uint64_t cap = static_cast<uint64_t>(sms) * 8;
     const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
     kern<<<grid, kSmallThreads, CRC ? kSmemSmall : 0, st>>>(a);

@@ -1,16 +1,17 @@
 // fcp_kernels.cuh — sm_100a kernels of the flash-checkpoint data path.
 //
 // Work decomposition: the packed image is cut into 16 KiB
-// regions = 32 rows of 512 B.  One warp owns one region at a time; in a row,
-// lane l owns the 16-byte word at row*512 + l*16, so every global access to
-// the packed image is a fully coalesced 512 B warp transaction.  There is no
-// CTA-level cooperation besides the shared CRC tables, so the grid is a
-// persistent set of warps striding over regions.
+// regions = 16 rows of 1 KiB.  One warp owns one region at a time; in a row,
+// lane l owns the 32-byte word at row*1024 + l*32 and moves it with one
+// 256-bit access (LDG.E.256 / STG.E.256, new on sm_100), so every global
+// access to the packed image is a fully coalesced 1 KiB warp transaction.
+// There is no CTA-level cooperation besides the shared CRC tables, so the
+// grid is a persistent set of warps striding over regions.
 //
 // Fused CRC-32C: lane l keeps a Horner accumulator over its column of words
-//     acc <- shift_496B(acc) ; acc <- crc32c_update(acc, word)       per row
-// (the 496 B shift brings the state from the end of the lane's previous word
-// to the start of its next one).  After 32 rows a 5-level warp tree combines
+//     acc <- shift_992B(acc) ; acc <- crc32c_update(acc, 8 x u32)     per row
+// (the 992 B shift brings the state from the end of the lane's previous word
+// to the start of its next one).  After 16 rows a 5-level warp tree combines
 // the 32 column values into the raw CRC of the region; a tiny second kernel
 // Horner-combines the regions of each chunk.  All of it is exact GF(2) linear
 // algebra, so the result is the standard CRC-32C of the chunk.
@@ -22,123 +23,183 @@
 
 namespace fcpk {
 
-constexpr int kRowBytes = 512;
-constexpr int kRows = 32;
+constexpr int kWordBytes = 32;
+constexpr int kRowBytes = 32 * kWordBytes;  // 1 KiB
+constexpr int kRows = 16;
 constexpr int kRegion = kRowBytes * kRows;  // == FCP_REGION_BYTES
 static_assert(kRegion == FCP_REGION_BYTES, "region size mismatch");
 
 // word offsets inside the device table blob
 constexpr int kTabT = 0;            // update by 4 data bytes  (shift 4 B)
-constexpr int kTabK = 1024;         // shift 496 B (row stride - word)
-constexpr int kTabC = 2048;         // 5 tables: shift 16,32,64,128,256 B
+constexpr int kTabK = 1024;         // shift 992 B (row stride - word)
+constexpr int kTabC = 2048;         // 5 tables: shift 32,64,128,256,512 B
 constexpr int kTabF = 2048 + 5120;  // shift one region (16 KiB)
 constexpr int kTabWords = kTabF + 1024;
 
 // per-device constant tables, filled once by fcp_init()
 static __device__ uint32_t g_fcp_tab[kTabWords];
 
+struct W8 {
+  uint32_t v[8];
+};
+
 // ---------------------------------------------------------------- memory ops
-__device__ __forceinline__ uint4 ld16_stream(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+__device__ __forceinline__ W8 ld32_stream(const void* p) {
+  W8 r;
+  asm volatile(
+      "ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]),
+        "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+      : "l"(p));
+  return r;
+}
+__device__ __forceinline__ W8 ld32(const void* p) {
+  W8 r;
+  asm volatile("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]),
+                 "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
                : "l"(p));
   return r;
 }
-__device__ __forceinline__ uint4 ld16(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
-  return r;
+__device__ __forceinline__ void st32(void* p, const W8& w) {
+  asm volatile("st.global.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p),
+               "r"(w.v[0]), "r"(w.v[1]), "r"(w.v[2]), "r"(w.v[3]), "r"(w.v[4]),
+               "r"(w.v[5]), "r"(w.v[6]), "r"(w.v[7])
+               : "memory");
 }
-__device__ __forceinline__ void st16(void* p, const uint4& v) {
-  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
-               "r"(v.y), "r"(v.z), "r"(v.w)
+__device__ __forceinline__ void st16(void* p, uint32_t a, uint32_t b,
+                                     uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b),
+               "r"(c), "r"(d)
                : "memory");
 }
 
-// bytes [mis, mis+16) of the 32-byte concatenation a||b, 0 < mis < 16
-__device__ __forceinline__ uint4 funnel16(const uint4& a, const uint4& b,
-                                          uint32_t mis) {
-  uint32_t x0, x1, x2, x3, x4;
-  switch (mis >> 2) {
-    case 0: x0 = a.x; x1 = a.y; x2 = a.z; x3 = a.w; x4 = b.x; break;
-    case 1: x0 = a.y; x1 = a.z; x2 = a.w; x3 = b.x; x4 = b.y; break;
-    case 2: x0 = a.z; x1 = a.w; x2 = b.x; x3 = b.y; x4 = b.z; break;
-    default: x0 = a.w; x1 = b.x; x2 = b.y; x3 = b.z; x4 = b.w; break;
+// ask the TMA unit to pull [p, p+bytes) into L2 (fire and forget); p and
+// bytes must be multiples of 16
+__device__ __forceinline__ void prefetch_l2(uintptr_t p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes)
+               : "memory");
+}
+
+// bytes [m, m+32) of the 64-byte concatenation lo||hi, 0 < m < 32
+__device__ __forceinline__ W8 extract32(const W8& lo, const W8& hi,
+                                        uint32_t m) {
+  uint32_t x[9];
+#define FCP_PICK(S)                                                        \
+  {                                                                        \
+    _Pragma("unroll") for (int i = 0; i < 9; ++i) x[i] =                   \
+        (S + i < 8) ? lo.v[(S + i) & 7] : hi.v[(S + i) & 7];               \
   }
-  const uint32_t sh = (mis & 3u) * 8u;
-  uint4 r;
-  r.x = __funnelshift_r(x0, x1, sh);
-  r.y = __funnelshift_r(x1, x2, sh);
-  r.z = __funnelshift_r(x2, x3, sh);
-  r.w = __funnelshift_r(x3, x4, sh);
+  switch (m >> 2) {
+    case 0: FCP_PICK(0) break;
+    case 1: FCP_PICK(1) break;
+    case 2: FCP_PICK(2) break;
+    case 3: FCP_PICK(3) break;
+    case 4: FCP_PICK(4) break;
+    case 5: FCP_PICK(5) break;
+    case 6: FCP_PICK(6) break;
+    default: FCP_PICK(7) break;
+  }
+#undef FCP_PICK
+  const uint32_t sh = (m & 3u) * 8u;
+  W8 r;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r.v[i] = __funnelshift_r(x[i], x[i + 1], sh);
   return r;
 }
 
-// store 16 bytes at an arbitrarily aligned address with the widest stores the
+// store 32 bytes at an arbitrarily aligned address with the widest stores the
 // alignment allows
-__device__ __forceinline__ void st16_unaligned(uintptr_t t, const uint4& v) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  if ((t & 15u) == 0) {
-    st16(reinterpret_cast<void*>(t), v);
+__device__ __forceinline__ void st32_unaligned(uintptr_t t, const W8& w) {
+  if ((t & 31u) == 0) {
+    st32(reinterpret_cast<void*>(t), w);
+  } else if ((t & 15u) == 0) {
+    st16(reinterpret_cast<void*>(t), w.v[0], w.v[1], w.v[2], w.v[3]);
+    st16(reinterpret_cast<void*>(t + 16), w.v[4], w.v[5], w.v[6], w.v[7]);
   } else if ((t & 3u) == 0) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) reinterpret_cast<uint32_t*>(t)[i] = w[i];
+    for (int i = 0; i < 8; ++i) reinterpret_cast<uint32_t*>(t)[i] = w.v[i];
   } else if ((t & 1u) == 0) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < 16; ++i)
       reinterpret_cast<uint16_t*>(t)[i] =
-          static_cast<uint16_t>(w[i >> 1] >> ((i & 1) * 16));
+          static_cast<uint16_t>(w.v[i >> 1] >> ((i & 1) * 16));
   } else {
 #pragma unroll
-    for (int i = 0; i < 16; ++i)
+    for (int i = 0; i < 32; ++i)
       reinterpret_cast<uint8_t*>(t)[i] =
-          static_cast<uint8_t>(w[i >> 2] >> ((i & 3) * 8));
+          static_cast<uint8_t>(w.v[i >> 2] >> ((i & 3) * 8));
   }
 }
 
 // ------------------------------------------------------------------- CRC ops
-// unreplicated 4x256 table lookup of a linear map
-__device__ __forceinline__ uint32_t lin4(const uint32_t* tab, uint32_t x) {
-  return tab[x & 0xffu] ^ tab[256 + ((x >> 8) & 0xffu)] ^
-         tab[512 + ((x >> 16) & 0xffu)] ^ tab[768 + (x >> 24)];
-}
-// REPL-way replicated copy (entry e of lane-copy r at e*REPL + r): with
-// REPL == 32 lane l only ever touches bank l, so lookups never conflict.
-template <int REPL>
-__device__ __forceinline__ uint32_t lin4r(const uint32_t* tab_lane,
-                                          uint32_t x) {
-  return tab_lane[(x & 0xffu) * REPL] ^
-         tab_lane[(256 + ((x >> 8) & 0xffu)) * REPL] ^
-         tab_lane[(512 + ((x >> 16) & 0xffu)) * REPL] ^
-         tab_lane[(768 + (x >> 24)) * REPL];
+// The lookup tables live in shared memory and are addressed in the shared
+// window directly (32-bit addresses, no generic-pointer arithmetic).  A table
+// of a linear map has 4 parts (one per input byte) of 256 entries; it is
+// replicated R ways with entry e of copy r at (e*R + r)*4 bytes.  With R == 32
+// lane l only ever touches bank l: no conflicts at all; with R == 16 two
+// lanes share a copy that spans two banks.
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
 }
 
-template <int REPL>
-__device__ __forceinline__ uint32_t crc_word(const uint32_t* sT_lane,
-                                             const uint32_t* sK, uint32_t acc,
-                                             const uint4& w) {
-  uint32_t s = lin4(sK, acc);
-  s = lin4r<REPL>(sT_lane, s ^ w.x);
-  s = lin4r<REPL>(sT_lane, s ^ w.y);
-  s = lin4r<REPL>(sT_lane, s ^ w.z);
-  s = lin4r<REPL>(sT_lane, s ^ w.w);
+template <int R>
+struct TabGeom {
+  static constexpr uint32_t kEntry = R * 4u;         // bytes between entries
+  static constexpr uint32_t kMask = 0xffu * kEntry;  // scaled byte index
+  static constexpr uint32_t kPart = 256u * kEntry;   // bytes per part
+  static constexpr int kLog = R == 32 ? 7 : R == 16 ? 6 : R == 8 ? 5 : 2;
+  static_assert((1u << kLog) == kEntry, "unsupported replication");
+};
+
+// `base` = shared address of the table, `lane_off` = (lane % R) * 4.  Each
+// lookup is shift + (and|or) + LDS [reg + uniform base + imm].
+template <int R>
+__device__ __forceinline__ uint32_t lin4s(uint32_t base, uint32_t lane_off,
+                                          uint32_t x) {
+  using G = TabGeom<R>;
+  const uint32_t o0 = ((x << G::kLog) & G::kMask) | lane_off;
+  const uint32_t o1 = ((x >> (8 - G::kLog)) & G::kMask) | lane_off;
+  const uint32_t o2 = ((x >> (16 - G::kLog)) & G::kMask) | lane_off;
+  const uint32_t o3 = ((x >> (24 - G::kLog)) & G::kMask) | lane_off;
+  return lds32(base + o0) ^ lds32(base + G::kPart + o1) ^
+         lds32(base + 2 * G::kPart + o2) ^ lds32(base + 3 * G::kPart + o3);
+}
+
+struct Tabs {
+  uint32_t T, K, C;     // shared addresses of the update, row-shift and
+                        // combine tables
+  uint32_t offT, offK;  // this lane's copy offsets
+};
+
+template <int RT, int RK>
+__device__ __forceinline__ uint32_t crc_word(const Tabs& t, uint32_t acc,
+                                             const W8& w) {
+  uint32_t s = lin4s<RK>(t.K, t.offK, acc);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s = lin4s<RT>(t.T, t.offT, s ^ w.v[i]);
   return s;
 }
 
 // combine the 32 column accumulators of a region; result valid in lane 31
-__device__ __forceinline__ uint32_t warp_combine(const uint32_t* sC,
-                                                 uint32_t acc, int lane) {
+__device__ __forceinline__ uint32_t warp_combine(const Tabs& t, uint32_t acc,
+                                                 int lane) {
 #pragma unroll
   for (int k = 0; k < 5; ++k) {
     const uint32_t recv = __shfl_up_sync(0xffffffffu, acc, 1u << k);
-    const uint32_t sh = lin4(sC + k * 1024, recv);
+    const uint32_t sh = lin4s<1>(t.C + k * 4096u, 0u, recv);
     const uint32_t m = (2u << k) - 1u;
     if ((static_cast<uint32_t>(lane) & m) == m) acc ^= sh;
   }
   return acc;
+}
+
+// global-memory flavour used by the finalize kernel (unreplicated table)
+__device__ __forceinline__ uint32_t lin4(const uint32_t* tab, uint32_t x) {
+  return tab[x & 0xffu] ^ tab[256 + ((x >> 8) & 0xffu)] ^
+         tab[512 + ((x >> 16) & 0xffu)] ^ tab[768 + (x >> 24)];
 }
 
 // -------------------------------------------------------- descriptor cursor
@@ -205,6 +266,7 @@ struct Args {
   uint64_t region_begin, region_end;
   uint8_t* packed;
   uint32_t* region_sums;
+  uint32_t run;  // regions per warp visit, set by the launcher
 };
 
 }  // namespace fcpk

@@ -2,94 +2,113 @@
 #pragma once
 #include "fcp_kernels.cuh"
 
+#ifndef FCP_ALIGNED_BATCH
+#define FCP_ALIGNED_BATCH 2
+#endif
+
+namespace fcpk {
+constexpr uint32_t kMaxRun = 8;  // consecutive regions per warp visit (<= 128 KiB)
+}
+
 namespace fcpk {
 
 // ---- word-level slow paths (tensor boundaries, gaps, tail of the image) ----
 
-// PACK: assemble the 16 packed bytes [o, o+16) from whatever descriptors
+// PACK: assemble the 32 packed bytes [o, o+32) from whatever descriptors
 // cover them; uncovered / out-of-range bytes are zero.
-__device__ __noinline__ uint4 gather_word(Cur& c, const fcp_desc* __restrict__ d,
-                                          uint32_t n, uint64_t o,
-                                          uint64_t total) {
-  uint32_t w[4] = {0u, 0u, 0u, 0u};
+__device__ __noinline__ W8 gather_word(Cur& c, const fcp_desc* __restrict__ d,
+                                       uint32_t n, uint64_t o, uint64_t total) {
+  W8 w;
 #pragma unroll
-  for (int b = 0; b < 16; ++b) {
+  for (int i = 0; i < 8; ++i) w.v[i] = 0u;
+#pragma unroll
+  for (int b = 0; b < kWordBytes; ++b) {
     const uint64_t p = o + b;
     if (p < total) {
       cur_seek(c, d, n, p);
       if (c.off <= p) {
         const uint32_t v = *reinterpret_cast<const uint8_t*>(c.ptr + (p - c.off));
-        w[b >> 2] |= v << ((b & 3) * 8);
+        w.v[b >> 2] |= v << ((b & 3) * 8);
       }
     }
   }
-  return make_uint4(w[0], w[1], w[2], w[3]);
+  return w;
 }
 
-// SCATTER: hand the 16 packed bytes [o, o+16) to whatever descriptors cover
+// SCATTER: hand the 32 packed bytes [o, o+32) to whatever descriptors cover
 // them, byte by byte.
 __device__ __noinline__ void scatter_word(Cur& c, const fcp_desc* __restrict__ d,
                                           uint32_t n, uint64_t o, uint64_t total,
-                                          const uint4& v) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                                          const W8& w) {
 #pragma unroll
-  for (int b = 0; b < 16; ++b) {
+  for (int b = 0; b < kWordBytes; ++b) {
     const uint64_t p = o + b;
     if (p < total) {
       cur_seek(c, d, n, p);
       if (c.off <= p)
         *reinterpret_cast<uint8_t*>(c.ptr + (p - c.off)) =
-            static_cast<uint8_t>(w[b >> 2] >> ((b & 3) * 8));
+            static_cast<uint8_t>(w.v[b >> 2] >> ((b & 3) * 8));
     }
   }
 }
 
-// zero the bytes of a packed word that lie at or beyond `total`
-__device__ __forceinline__ uint4 mask_tail(const uint4& v, uint64_t o,
-                                           uint64_t total) {
-  if (o + 16 <= total) return v;
-  uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  const int valid = (o >= total) ? 0 : static_cast<int>(total - o);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int vb = valid - i * 4;  // valid bytes of this 32-bit word
-    if (vb <= 0) w[i] = 0u;
-    else if (vb < 4) w[i] &= (1u << (vb * 8)) - 1u;
-  }
-  return make_uint4(w[0], w[1], w[2], w[3]);
-}
-
 // store a packed word whose tail may stick out of the image (PACK side)
 __device__ __forceinline__ void store_packed(uint8_t* packed, uint64_t o,
-                                             uint64_t total, const uint4& v) {
-  if (o + 16 <= total) {
-    st16(packed + o, v);
+                                             uint64_t total, const W8& w) {
+  if (o + kWordBytes <= total) {
+    st32(packed + o, w);
   } else {
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    for (int b = 0; b < 16 && o + b < total; ++b)
-      packed[o + b] = static_cast<uint8_t>(w[b >> 2] >> ((b & 3) * 8));
+#pragma unroll
+    for (int b = 0; b < kWordBytes; ++b)
+      if (o + b < total)
+        packed[o + b] = static_cast<uint8_t>(w.v[b >> 2] >> ((b & 3) * 8));
   }
+}
+
+// load the packed word at offset o (SCATTER side); a word that straddles the
+// end of the image is read byte by byte so no byte beyond `total` is touched
+// (bytes beyond it count as zero for the checksum)
+__device__ __forceinline__ W8 load_packed(const uint8_t* packed, uint64_t o,
+                                          uint64_t total) {
+  if (o + kWordBytes <= total) return ld32_stream(packed + o);
+  W8 w;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) w.v[i] = 0u;
+#pragma unroll
+  for (int b = 0; b < kWordBytes; ++b)
+    if (o + b < total)
+      w.v[b >> 2] |= static_cast<uint32_t>(packed[o + b]) << ((b & 3) * 8);
+  return w;
 }
 
 // ---------------------------------------------------------------- the kernel
 // PACK = true : tensors -> packed image   (desc.ptr is the source)
 // PACK = false: packed image -> tensors   (desc.ptr is the target)
-// REPL: replication of the 4-byte update table in shared memory (1 or 32).
+// REPL: replication of the 4-byte update table in shared memory (1 or 32);
+// the row-shift table is replicated REPL/2 ways.
 template <bool PACK, bool CRC, int REPL, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
+  constexpr int RK = REPL > 1 ? REPL / 2 : 1;
+  constexpr int kBatch = FCP_ALIGNED_BATCH;
   extern __shared__ uint32_t smem[];
-  uint32_t* sT = smem;                    // 1024 * REPL words
-  uint32_t* sK = smem + 1024 * REPL;      // 1024 words
-  uint32_t* sC = sK + 1024;               // 5120 words
+  uint32_t* sT = smem;              // 1024 * REPL words
+  uint32_t* sK = sT + 1024 * REPL;  // 1024 * RK words
+  uint32_t* sC = sK + 1024 * RK;    // 5120 words
   if (CRC) {
     for (int i = threadIdx.x; i < 1024 * REPL; i += THREADS)
       sT[i] = g_fcp_tab[kTabT + i / REPL];
-    for (int i = threadIdx.x; i < 1024 + 5120; i += THREADS)
-      sK[i] = g_fcp_tab[kTabK + i];
+    for (int i = threadIdx.x; i < 1024 * RK; i += THREADS)
+      sK[i] = g_fcp_tab[kTabK + i / RK];
+    for (int i = threadIdx.x; i < 5120; i += THREADS) sC[i] = g_fcp_tab[kTabC + i];
     __syncthreads();
   }
   const int lane = threadIdx.x & 31;
-  const uint32_t* sT_lane = sT + (REPL == 32 ? lane : 0);
+  Tabs tb;
+  tb.T = static_cast<uint32_t>(__cvta_generic_to_shared(sT));
+  tb.K = static_cast<uint32_t>(__cvta_generic_to_shared(sK));
+  tb.C = static_cast<uint32_t>(__cvta_generic_to_shared(sC));
+  tb.offT = static_cast<uint32_t>(lane % REPL) * 4u;
+  tb.offK = static_cast<uint32_t>(lane % RK) * 4u;
   const uint64_t warps_total =
       static_cast<uint64_t>(gridDim.x) * (THREADS / 32);
   const uint64_t gwarp =
@@ -98,67 +117,73 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   const uint32_t n = a.n_desc;
   const uint64_t total = a.total;
 
-  for (uint64_t r = a.region_begin + gwarp; r < a.region_end; r += warps_total) {
+  // A warp takes runs of a.run consecutive regions: the descriptor search is
+  // paid once per run, inside a run the cursor just walks forward.
+  const uint64_t kRun = a.run;
+  const uint64_t n_runs = (a.region_end - a.region_begin + kRun - 1) / kRun;
+  for (uint64_t run = gwarp; run < n_runs; run += warps_total) {
+   const uint64_t run_begin = a.region_begin + run * kRun;
+   const uint64_t run_end =
+       run_begin + kRun < a.region_end ? run_begin + kRun : a.region_end;
+   Cur c;
+   c.idx = warp_first_desc(descs, n, run_begin * kRegion, lane);
+   cur_load(c, descs, n);
+   for (uint64_t r = run_begin; r < run_end; ++r) {
     const uint64_t rbase = r * kRegion;
-    Cur c;
-    c.idx = warp_first_desc(descs, n, rbase, lane);
-    cur_load(c, descs, n);
+    cur_seek(c, descs, n, rbase);  // same answer in every lane
     uint32_t acc = 0;
-    const uint64_t lane_o = rbase + static_cast<uint64_t>(lane) * 16;
+    const uint64_t lane_o = rbase + static_cast<uint64_t>(lane) * kWordBytes;
 
     // Whole region inside one tensor (uniform across the warp): no per-word
     // descriptor logic, loads batched for memory-level parallelism.
     const bool whole = (c.off <= rbase) && (rbase + kRegion <= c.end);
     if (whole) {
-      const uintptr_t t0 = c.ptr + (rbase - c.off) + lane * 16;  // tensor side
-      uint8_t* p0 = a.packed + lane_o;                           // packed side
-      const uint32_t mis = static_cast<uint32_t>(t0 & 15u);
-      if (PACK) {
-        if (mis == 0) {
+      const uintptr_t t0 = c.ptr + (rbase - c.off) + lane * kWordBytes;  // tensor side
+      uint8_t* p0 = a.packed + lane_o;                                   // packed side
+      const uint32_t mis = static_cast<uint32_t>(t0 & 31u);
+      // read side of this region, seen by lane 0 (16-byte aligned down): the
+      // batch after the one being loaded is prefetched into L2 by one bulk
+      // request, so the 256-bit loads mostly hit L2 instead of waiting on HBM
+      const uintptr_t rd0 = (PACK ? c.ptr + (rbase - c.off)
+                                  : reinterpret_cast<uintptr_t>(a.packed + rbase)) & ~uintptr_t(15);
+      if (PACK && mis != 0) {
+        // source not 32-byte aligned relative to the image: fetch the two
+        // aligned words around each word (the second is the next lane's
+        // first: an L1 hit) and realign in registers
+        const uintptr_t ta = t0 - mis;
 #pragma unroll 1
-          for (int row = 0; row < kRows; row += 8) {
-            uint4 v[8];
+        for (int row = 0; row < kRows; row += 2) {
+          if (lane == 0 && row + 2 < kRows)
+            prefetch_l2(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 64);
+          W8 lo[2], hi[2];
 #pragma unroll
-            for (int k = 0; k < 8; ++k)
-              v[k] = ld16_stream(reinterpret_cast<const void*>(
-                  t0 + (row + k) * kRowBytes));
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              st16(p0 + (row + k) * kRowBytes, v[k]);
-              if (CRC) acc = crc_word<REPL>(sT_lane, sK, acc, v[k]);
-            }
+          for (int k = 0; k < 2; ++k) {
+            lo[k] = ld32(reinterpret_cast<const void*>(ta + (row + k) * kRowBytes));
+            hi[k] = ld32(reinterpret_cast<const void*>(
+                ta + (row + k) * kRowBytes + kWordBytes));
           }
-        } else {
-          const uintptr_t ta = t0 - mis;
-#pragma unroll 1
-          for (int row = 0; row < kRows; row += 4) {
-            uint4 lo[4], hi[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              lo[k] = ld16(reinterpret_cast<const void*>(
-                  ta + (row + k) * kRowBytes));
-              hi[k] = ld16(reinterpret_cast<const void*>(
-                  ta + (row + k) * kRowBytes + 16));
-            }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint4 v = funnel16(lo[k], hi[k], mis);
-              st16(p0 + (row + k) * kRowBytes, v);
-              if (CRC) acc = crc_word<REPL>(sT_lane, sK, acc, v);
-            }
+          for (int k = 0; k < 2; ++k) {
+            const W8 v = extract32(lo[k], hi[k], mis);
+            st32(p0 + (row + k) * kRowBytes, v);
+            if (CRC) acc = crc_word<REPL, RK>(tb, acc, v);
           }
         }
       } else {
+        const uintptr_t src = PACK ? t0 : reinterpret_cast<uintptr_t>(p0);
 #pragma unroll 1
-        for (int row = 0; row < kRows; row += 8) {
-          uint4 v[8];
+        for (int row = 0; row < kRows; row += kBatch) {
+          if (lane == 0 && row + kBatch < kRows)
+            prefetch_l2(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16);
+          W8 v[kBatch];
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            v[k] = ld16_stream(p0 + (row + k) * kRowBytes);
+          for (int k = 0; k < kBatch; ++k)
+            v[k] = ld32(reinterpret_cast<const void*>(src + (row + k) * kRowBytes));
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            st16_unaligned(t0 + (row + k) * kRowBytes, v[k]);
-            if (CRC) acc = crc_word<REPL>(sT_lane, sK, acc, v[k]);
+          for (int k = 0; k < kBatch; ++k) {
+            if (PACK) st32(p0 + (row + k) * kRowBytes, v[k]);
+            else st32_unaligned(t0 + (row + k) * kRowBytes, v[k]);
+            if (CRC) acc = crc_word<REPL, RK>(tb, acc, v[k]);
           }
         }
       }
@@ -167,43 +192,45 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
 #pragma unroll 1
       for (int row = 0; row < kRows; ++row) {
         const uint64_t o = lane_o + static_cast<uint64_t>(row) * kRowBytes;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        W8 v;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v.v[i] = 0u;
         if (o < total) {
           cur_seek(c, descs, n, o);
-          const bool interior = (c.off <= o) && (o + 16 <= c.end);
+          const bool interior = (c.off <= o) && (o + kWordBytes <= c.end);
           if (PACK) {
             if (interior) {
               const uintptr_t t = c.ptr + (o - c.off);
-              const uint32_t mis = static_cast<uint32_t>(t & 15u);
+              const uint32_t mis = static_cast<uint32_t>(t & 31u);
               if (mis == 0) {
-                v = ld16_stream(reinterpret_cast<const void*>(t));
+                v = ld32_stream(reinterpret_cast<const void*>(t));
               } else {
-                const uint4 lo = ld16(reinterpret_cast<const void*>(t - mis));
-                const uint4 hi =
-                    ld16(reinterpret_cast<const void*>(t - mis + 16));
-                v = funnel16(lo, hi, mis);
+                const W8 lo = ld32(reinterpret_cast<const void*>(t - mis));
+                const W8 hi = ld32(reinterpret_cast<const void*>(t - mis + kWordBytes));
+                v = extract32(lo, hi, mis);
               }
-              st16(a.packed + o, v);
+              st32(a.packed + o, v);
             } else {
               v = gather_word(c, descs, n, o, total);
               store_packed(a.packed, o, total, v);
             }
           } else {
-            v = mask_tail(ld16_stream(a.packed + o), o, total);
+            v = load_packed(a.packed, o, total);
             if (interior)
-              st16_unaligned(c.ptr + (o - c.off), v);
+              st32_unaligned(c.ptr + (o - c.off), v);
             else
               scatter_word(c, descs, n, o, total, v);
           }
         }
-        if (CRC) acc = crc_word<REPL>(sT_lane, sK, acc, v);
+        if (CRC) acc = crc_word<REPL, RK>(tb, acc, v);
       }
       __syncwarp();
     }
     if (CRC) {
-      acc = warp_combine(sC, acc, lane);
+      acc = warp_combine(tb, acc, lane);
       if (lane == 31) a.region_sums[r] = acc;
     }
+   }
   }
 }
 
