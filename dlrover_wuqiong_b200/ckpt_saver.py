@@ -857,7 +857,9 @@ class FsdpDcpSaver(CommonDirCheckpointSaver):
         handler = self._shm_handlers[local_shard_id]
         path = ckpt_config.paths[CheckpointConstant.MODEL_STATES_NAME]
         checkpoint_dir = os.path.dirname(path)
-        self._dist_make_dir(checkpoint_dir)
+        # (the reference calls _dist_make_dir here, whose rmtree lets the
+        # shards of one node delete each other's files; SAVER:1181-1185)
+        self.storage.safe_makedirs(checkpoint_dir)
         assert handler.shared_memory is not None
         self.storage.write(handler.shared_memory.buf, path)
         if self._is_agent_rank_0 and local_shard_id == 0:
