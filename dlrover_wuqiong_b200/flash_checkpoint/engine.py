@@ -356,3 +356,39 @@ class CheckpointEngine(metaclass=ABCMeta):
     @abstractmethod
     def load(self, resume_path=""):
         """State dict from shm if valid, else from storage."""
+
+
+class LocalShardsEngine(CheckpointEngine):
+    """Common shape of the DeepSpeed and Megatron engines: there are
+    ``get_global_shard_num()`` shards in the job, the first
+    ``min(local_world_size, global_shard_num)`` local ranks of every node each
+    own one, and after a successful save one rank per node tells its agent to
+    persist (deepspeed_engine.py:61-135, megatron_engine.py:73-146)."""
+
+    def get_saving_ranks(self):
+        per_node = env_utils.get_local_world_size()
+        shards = self.get_local_shard_num()
+        return [r for r in range(dist.get_world_size()) if r % per_node < shards]
+
+    def get_local_shard_num(self):
+        return min(env_utils.get_local_world_size(), self.get_global_shard_num())
+
+    @timer
+    def save_to_memory(self, step, state_dict, paths):
+        conf = CheckpointConfig(step=step, paths=paths)
+        return self.save_state_dict_to_memory(state_dict, conf)
+
+    def _notifies_agent(self):
+        """Whether this rank puts the SAVE event after a save."""
+        return self._local_rank == 0
+
+    @timer
+    def save_to_storage(self, step, state_dict, paths):
+        success = True
+        if step > self._cached_step:
+            success = self.save_to_memory(step, state_dict, paths)
+        if dist.is_initialized():
+            dist.barrier()
+        if success and self._notifies_agent():
+            self._event_queue.put(CheckpointEvent(type=CheckpointEventType.SAVE, step=step))
+        return success
