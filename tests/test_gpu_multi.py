@@ -1,0 +1,123 @@
+"""GPU, 2 ranks over NCCL (skipped on a 1-GPU box): recovery of a replaced
+rank of a replicated DDP group from the packed image a surviving peer still
+holds in HBM — NCCL broadcast over NVLink, then the scatter kernel with CRC
+verification (replaces the gloo/CPU broadcast of
+dlrover/trainer/torch/flash_checkpoint/replica.py:275-332) — and every rank
+checkpointing its own shard concurrently."""
+import os
+import socket
+import sys
+import tempfile
+import traceback
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, run_id, tmpdir, errq):
+    try:
+        if ROOT not in sys.path:
+            sys.path.insert(0, ROOT)
+        os.environ.update({
+            "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank),
+            "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank), "LOCAL_WORLD_SIZE": str(world),
+            "NODE_NUM": "1", "NODE_RANK": "0", "ROLE_NAME": "dlrover-trainer",
+            "TORCHELASTIC_RUN_ID": run_id, "DLROVER_LOG_LEVEL": "WARNING"})
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", rank))
+        from dlrover_wuqiong_b200.ckpt_saver import (DLROVER_CKPT_CONFIG_KEY,
+                                                     AsyncCheckpointSaver, CheckpointConfig,
+                                                     SharedMemoryHandler)
+        from dlrover_wuqiong_b200.flash_checkpoint.ddp import DdpCheckpointer, StorageType
+        from dlrover_wuqiong_b200.flash_checkpoint.replica import FullCkptReplicaManager
+        if rank == 0:
+            AsyncCheckpointSaver.start_async_saving_ckpt()
+
+        # --- every rank saves / restores its own shard at the same time
+        torch.manual_seed(100 + rank)
+        model = nn.Sequential(nn.Linear(1024, 2048), nn.Linear(2048, 512)).cuda()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-3, fused=True)
+        model(torch.randn(4, 1024, device="cuda")).sum().backward()
+        opt.step()
+        ckpt = DdpCheckpointer(tmpdir, local_shard_num=world, global_shard_num=world)
+        sd = {"model": model.state_dict(), "optimizer": opt.state_dict(), "step": 3}
+        want = {k: v.clone() for k, v in model.state_dict().items()}
+        assert ckpt.save_checkpoint(3, sd, storage_type=StorageType.MEMORY)
+        with torch.no_grad():
+            for p in model.parameters():
+                p.zero_()
+        ckpt.load_checkpoint(into=sd)
+        for k, v in want.items():
+            assert torch.equal(model.state_dict()[k], v), k
+        ckpt.close()
+
+        # --- replicated group: rank 1 was replaced and has nothing in memory
+        torch.manual_seed(7)
+        rep = nn.Sequential(nn.Linear(777, 1333), nn.Linear(1333, 91)).cuda()
+        ropt = torch.optim.AdamW(rep.parameters(), lr=1e-3, fused=True)
+        rep(torch.randn(4, 777, device="cuda")).sum().backward()
+        ropt.step()
+        rsd = {"model": rep.state_dict(), "optimizer": ropt.state_dict(), "step": 11}
+        rwant = {k: v.clone() for k, v in rep.state_dict().items()}
+        handler = SharedMemoryHandler(10 + rank, host=True)
+        if rank == 0:
+            full = dict(rsd)
+            full[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=11, rank=0, world_size=world)
+            handler.save_state_dict(full)
+        else:
+            with torch.no_grad():  # the replacement starts from garbage
+                for p in rep.parameters():
+                    p.fill_(-1.0)
+        mgr = FullCkptReplicaManager(replica_count=0)
+        step = mgr.recover_on_device(handler, rsd, healthy=(rank == 0))
+        assert step == 11
+        for k, v in rwant.items():
+            assert torch.equal(rep.state_dict()[k], v), k
+        dist.barrier()
+        if rank == 0:
+            handler.unlink()
+            saver = AsyncCheckpointSaver.get_ckpt_saver()
+            if saver:
+                saver.close()
+        handler.close()
+        dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        errq.put("rank %d:\n%s" % (rank, traceback.format_exc()))
+        raise
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_nccl_save_restore_and_peer_recovery():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    ctx = mp.get_context("spawn")
+    errq = ctx.SimpleQueue()
+    port, run_id = _free_port(), "fcp_gpu2_%d" % os.getpid()
+    with tempfile.TemporaryDirectory() as tmpdir:
+        procs = [ctx.Process(target=_worker, args=(r, 2, port, run_id, tmpdir, errq))
+                 for r in range(2)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(240)
+        alive = [p for p in procs if p.is_alive()]
+        for p in alive:
+            p.kill()
+        errors = []
+        while not errq.empty():
+            errors.append(errq.get())
+        assert not alive, "workers hung"
+        assert not errors and all(p.exitcode == 0 for p in procs), "\n".join(errors)
