@@ -214,6 +214,39 @@ def cpu_reference_steps(workload, steps, warmup, sample_bytes):
     return 2 * total / dt / GB, dt, sample, torch.get_num_threads()
 
 
+def reference_loop_on_gpu_tensors(sd, sample_bytes):
+    """SAVER:174-206 / 112-137 (oracle port) with the tensors on the GPU: one
+    synchronous pageable D2H per tensor on save, one pageable H2D per tensor
+    on restore."""
+    from oracle import oracle
+    model, state, used = {}, {}, 0
+    for i, (name, w) in enumerate(sd["model"].items()):
+        if i not in sd["optimizer"]["state"]:
+            break
+        if used + w.numel() * 12 > sample_bytes and model:
+            break
+        model[name] = w
+        state[i] = sd["optimizer"]["state"][i]
+        used += w.numel() * 12 + 4
+    sample = {"model": model, "optimizer": {"state": state}}
+    meta, total = oracle.layout(sample)
+    mm = mmap.mmap(-1, total, flags=mmap.MAP_SHARED | mmap.MAP_POPULATE)
+    times = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        oracle.ref_save_into(sample, meta, mm)
+        oracle.ref_load_from(meta, mm, sample)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+    mm.close()
+    dt = min(times[1:])
+    return {"value": 2 * total / dt / GB, "unit": "GB/s", "s_per_step": dt,
+            "sample": "prefix of the bench state: %d tensors, %.2f GB, save+restore"
+                      % (len(oracle.flatten(sample)[0]), total / GB),
+            "what": "reference per-tensor torch copy_ loop, CUDA tensors <-> pageable mapping"}
+
+
 # ------------------------------------------------------------------ helpers
 def _dist_max(x, device):
     if not dist.is_initialized():
@@ -399,6 +432,20 @@ def run_ours(args, rank, local_rank, world):
         pending.wait()
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- leg 4: cold restore — what a restarted trainer sees: attach to the
+    # existing segment (not pinned in this "new" process) and restore
+    from dlrover_wuqiong_b200.ckpt_saver import SharedMemoryHandler
+    handler._drop_engine()  # forget plan, staging and the pinned mapping
+    _barrier_sync(device)
+    fresh = SharedMemoryHandler(ckpt._engine.local_shard_id, host=False)
+    t0 = time.perf_counter()
+    fresh.load_state_dict(into={"model_states": sd})
+    torch.cuda.synchronize(device)
+    restore_cold_s = _dist_max(time.perf_counter() - t0, device)
+    cold_path = fresh.last_stats.get("restore_path")
+    fresh.close()
+    _barrier_sync(device)
+
     save_blocking_s = _dist_max(statistics.median(block_s), device)
     save_pack_ms = _dist_max(statistics.median(pack_ms), device)
     save_durable_ms = _dist_max(statistics.median(save_ms), device)
@@ -407,6 +454,13 @@ def run_ours(args, rank, local_rank, world):
     ms_per_step = dev_ms / K
     value = world * 2 * B / (ms_per_step / 1e3) / GB
     e2e_value = world * 2 * B / (e2e_s / K) / GB
+
+    # the true "before" on GPU-resident state: the reference's per-tensor
+    # pageable copy_ loop (oracle port) fed with CUDA tensors, on a prefix of
+    # the very same state dict
+    ref_gpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ref_gpu = reference_loop_on_gpu_tensors(sd, int(args.cpu_sample_gb * GB))
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -432,6 +486,8 @@ def run_ours(args, rank, local_rank, world):
             "save_blocking_device_s": save_pack_ms / 1e3,
             "save_durable_s": save_durable_ms / 1e3,
             "restore_s": restore_med_ms / 1e3,
+            "restore_cold_s": restore_cold_s, "restore_cold_path": cold_path,
+            "restore_cold_GBps_per_rank": B / restore_cold_s / GB,
             "save_GBps_per_rank": B / (save_durable_ms / 1e3) / GB,
             "restore_GBps_per_rank": B / (restore_med_ms / 1e3) / GB,
             "host_link_frac": {"save": B / (save_durable_ms / 1e3) / GB / PCIE_GEN5_X16_GBS,
@@ -442,6 +498,7 @@ def run_ours(args, rank, local_rank, world):
                          "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch_set": 2 * B},
             "cpu_baseline": cpu_base,
+            "reference_loop_gpu_source": ref_gpu,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": B,
                     "d2h_bytes_per_step": B, "s_per_step": e2e_s / K,
                     "api": "DdpCheckpointer.save_checkpoint(MEMORY) + load_checkpoint(into=)"},

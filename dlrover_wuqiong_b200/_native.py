@@ -46,6 +46,7 @@ SYMBOLS = [
     ("fcp_save_packed_wait", _i, [_vp]),
     ("fcp_save_wait", _i, [_vp, _vp]),
     ("fcp_restore", _i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
+    ("fcp_restore_bounced", _i, [_vp, _vp, _vp, _i, _vp, _i, _vp]),
     ("fcp_restore_from_device", _i, [_vp, _vp, _i, _vp, _vp]),
     ("fcp_plan_timings", _i, [_vp, _vp]),
     ("fcp_plan_last_launches", _u64, [_vp]),
@@ -159,6 +160,17 @@ class Plan:
                 raise ValueError("expected %d checksums, got %d" % (self.num_chunks, len(exp)))
         check(lib().fcp_restore(self._h, host_ptr, staging_ptr, mode, checksum,
                                 exp.ctypes.data if exp is not None else None, stream))
+
+    def restore_bounced(self, host_ptr, staging_ptr, checksum=SUM_CRC32C, expected=None,
+                        n_workers=0, stream=0):
+        exp = None
+        if expected is not None:
+            exp = np.ascontiguousarray(expected, dtype=np.uint32)
+            if len(exp) != self.num_chunks:
+                raise ValueError("expected %d checksums, got %d" % (self.num_chunks, len(exp)))
+        check(lib().fcp_restore_bounced(self._h, host_ptr, staging_ptr, checksum,
+                                        exp.ctypes.data if exp is not None else None,
+                                        n_workers, stream))
 
     def restore_from_device(self, packed_ptr, checksum=SUM_CRC32C, expected=None, stream=0):
         exp = None

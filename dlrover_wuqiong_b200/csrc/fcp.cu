@@ -8,7 +8,9 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <mutex>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -194,6 +196,10 @@ struct fcp_plan {
   bool last_has_sums = false;
   bool save_in_flight = false;
   int save_mode = 0;
+  // pinned bounce ring of fcp_restore_bounced: 2 slots per worker
+  uint8_t* ring = nullptr;
+  uint64_t ring_slot_bytes = 0;
+  int ring_workers = 0;
 };
 
 namespace {
@@ -386,6 +392,7 @@ void fcp_plan_destroy(fcp_plan* p) {
   if (p->d_region_sums) cudaFree(p->d_region_sums);
   if (p->d_chunk_sums) cudaFree(p->d_chunk_sums);
   if (p->h_chunk_sums) cudaFreeHost(p->h_chunk_sums);
+  if (p->ring) cudaFreeHost(p->ring);
   if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   cudaEvent_t evs[] = {p->ev_begin, p->ev_packed, p->ev_done, p->ev_kern_b,
                        p->ev_kern_e};
@@ -706,6 +713,100 @@ int fcp_restore_from_device(fcp_plan* p, const void* packed, int checksum,
   FCP_CUDA(cudaEventSynchronize(p->ev_done));
   FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
   p->t_kernel_ms = p->t_total_ms;
+  p->t_copy_ms = 0.f;
+  p->last_has_sums = checksum != 0;
+  if (expected) return verify_sums(p, expected);
+  return 0;
+}
+
+int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
+                        int checksum, const uint32_t* expected, int n_workers,
+                        void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
+  if ((!host_src || !staging) && p->total)
+    return fail(-EINVAL, "host_src and staging are required");
+  if (expected && !checksum)
+    return fail(-EINVAL, "expected sums given but checksum disabled");
+  if (n_workers <= 0) {
+    unsigned hc = std::thread::hardware_concurrency();
+    n_workers = hc >= 16 ? 8 : hc >= 4 ? static_cast<int>(hc / 2) : 1;
+  }
+  if (n_workers > 32) n_workers = 32;
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  const uint64_t slot = 32ull << 20;
+  if (!p->ring || p->ring_workers < n_workers || p->ring_slot_bytes != slot) {
+    if (p->ring) cudaFreeHost(p->ring);
+    p->ring = nullptr;
+    FCP_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&p->ring),
+                           slot * 2 * static_cast<uint64_t>(n_workers),
+                           cudaHostAllocPortable));
+    p->ring_workers = n_workers;
+    p->ring_slot_bytes = slot;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  FCP_CUDA(cudaStreamSynchronize(st));  // staging is free, caller's work done
+  const uint64_t n_slices = ceil_div(p->total, slot);
+  std::atomic<uint64_t> next{0};
+  std::atomic<int> failed{0};
+  const uint8_t* src = static_cast<const uint8_t*>(host_src);
+  uint8_t* dst = static_cast<uint8_t*>(staging);
+  const int device = p->device;
+  uint8_t* ring = p->ring;
+  const uint64_t total = p->total;
+  auto worker = [&, device, ring, total](int w) {
+    if (cudaSetDevice(device) != cudaSuccess) { failed = 1; return; }
+    cudaStream_t ws = nullptr;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    if (cudaStreamCreateWithFlags(&ws, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming) != cudaSuccess) {
+      failed = 1;
+    }
+    uint64_t k = 0;
+    while (!failed) {
+      const uint64_t i = next.fetch_add(1);
+      if (i >= n_slices) break;
+      const int sl = static_cast<int>(k & 1);
+      uint8_t* buf = ring + (static_cast<uint64_t>(w) * 2 + sl) * slot;
+      if (k >= 2 && cudaEventSynchronize(ev[sl]) != cudaSuccess) { failed = 1; break; }
+      const uint64_t off = i * slot;
+      const uint64_t len = off + slot <= total ? slot : total - off;
+      memcpy(buf, src + off, len);  // page cache -> pinned
+      if (cudaMemcpyAsync(dst + off, buf, len, cudaMemcpyHostToDevice, ws) != cudaSuccess ||
+          cudaEventRecord(ev[sl], ws) != cudaSuccess) {
+        failed = 1;
+        break;
+      }
+      ++k;
+    }
+    if (ws) cudaStreamSynchronize(ws);
+    if (ev[0]) cudaEventDestroy(ev[0]);
+    if (ev[1]) cudaEventDestroy(ev[1]);
+    if (ws) cudaStreamDestroy(ws);
+  };
+  {
+    std::vector<std::thread> pool;
+    for (int w = 0; w < n_workers; ++w) pool.emplace_back(worker, w);
+    for (auto& t : pool) t.join();
+  }
+  if (failed) {
+    cudaGetLastError();
+    return fail(-EIO, "bounced host->device copy failed");
+  }
+  p->last_launches = 0;
+  int rc = plan_launch(p, staging, 1, checksum, 0, p->n_chunks, st);
+  if (rc) return rc;
+  if (checksum && p->n_chunks)
+    FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                             sizeof(uint32_t) * p->n_chunks,
+                             cudaMemcpyDeviceToHost, st));
+  FCP_CUDA(cudaEventRecord(p->ev_done, st));
+  FCP_CUDA(cudaEventSynchronize(p->ev_done));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
+  p->t_kernel_ms = 0.f;
   p->t_copy_ms = 0.f;
   p->last_has_sums = checksum != 0;
   if (expected) return verify_sums(p, expected);

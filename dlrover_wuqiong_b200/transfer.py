@@ -9,6 +9,7 @@ require libfcp.so and a CUDA device, or an exception is raised.
 """
 import ctypes
 import os
+import threading
 import time
 
 import numpy as np
@@ -69,6 +70,7 @@ class DeviceShardEngine(object):
         self._arena_dev = None
         self._arena_pin = None
         self._mapping = None
+        self._mapping_job = None  # background registration after a cold restore
         self._keepalive = []
         self.stats = {}
 
@@ -146,7 +148,28 @@ class DeviceShardEngine(object):
             self._staging = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self._plan
 
+    def _join_mapping_job(self):
+        job = self._mapping_job
+        if job is not None:
+            job.join()
+            self._mapping_job = None
+
+    def _register_in_background(self, buf, total):
+        """Pin the segment off the critical path (a restarted trainer's first
+        save would otherwise pay ~0.08 s/GB for it)."""
+        def run():
+            try:
+                with torch.cuda.device(self.device):
+                    self._mapping = HostMapping(buf, total)
+                    self.stats["register_s"] = self._mapping.register_s
+            except Exception as e:  # noqa: BLE001 - retried synchronously by the next save
+                logger.warning("background registration of the shm failed: %s", e)
+
+        self._mapping_job = threading.Thread(target=run, name="fcp-register", daemon=True)
+        self._mapping_job.start()
+
     def _ensure_mapping(self, buf, total):
+        self._join_mapping_job()
         addr = buffer_address(buf)
         if self._mapping is not None and (self._mapping.addr != addr
                                           or self._mapping.nbytes < total):
@@ -192,11 +215,29 @@ class DeviceShardEngine(object):
                     raise ValueError("restore target must be contiguous")
             ptrs, offs, sizes, host = self._sources(leaves)
             plan = self._ensure_plan(ptrs, offs, sizes, total)
-            addr = self._ensure_mapping(buf, total)
             stream = torch.cuda.current_stream(self.device)
             staging_ptr = self._staging.data_ptr() if self._staging is not None else None
             checksum = self.checksum if expected is not None else _native.SUM_NONE
-            plan.restore(addr, staging_ptr, self.mode, checksum, expected, stream.cuda_stream)
+            self._join_mapping_job()
+            cold = (self._mapping is None or self._mapping.addr != buffer_address(buf)
+                    or self._mapping.nbytes < total)
+            if (cold and total and self.mode == _native.MODE_STAGED
+                    and os.getenv("FCP_COLD_RESTORE", "bounce") == "bounce"):
+                # fresh process, segment not pinned yet: stream it through the
+                # pinned ring now, pin it in the background for later saves
+                if self._mapping is not None:
+                    self._mapping.close()
+                    self._mapping = None
+                plan.restore_bounced(buffer_address(buf), staging_ptr, checksum, expected,
+                                     int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
+                                     stream.cuda_stream)
+                self.stats["restore_path"] = "bounced"
+                self._register_in_background(buf, total)
+            else:
+                addr = self._ensure_mapping(buf, total)
+                plan.restore(addr, staging_ptr, self.mode, checksum, expected,
+                             stream.cuda_stream)
+                self.stats["restore_path"] = "registered"
             self._stage_host_leaves(host, to_device=False)
             self.stats.update(self._plan.timings())
 
@@ -221,6 +262,7 @@ class DeviceShardEngine(object):
                 torch.cuda.synchronize(self.device)
         except Exception:  # noqa: BLE001
             pass
+        self._join_mapping_job()
         if self._plan is not None:
             self._plan.close()
             self._plan = None

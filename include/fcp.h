@@ -199,6 +199,18 @@ int fcp_save_wait(fcp_plan* plan, uint32_t* chunk_sums);
 int fcp_restore(fcp_plan* plan, const void* host_src, void* staging, int mode,
                 int checksum, const uint32_t* expected, void* stream);
 
+/* Same result as fcp_restore in staged mode, for a host image that is NOT
+ * registered — the situation of a freshly restarted trainer attaching to the
+ * shm segment its predecessor left (SAVER:305-306).  Pinning 19 GB takes
+ * ~1.6 s (cudaHostRegister does not parallelise), so instead `n_workers` host
+ * threads (<= 0: pick from the core count) copy 32 MiB slices of the image
+ * into a small pinned ring owned by the plan and DMA them from there;
+ * the scatter kernel then verifies and unpacks the staged image.
+ * Synchronous.                                                              */
+int fcp_restore_bounced(fcp_plan* plan, const void* host_src, void* staging,
+                        int checksum, const uint32_t* expected, int n_workers,
+                        void* stream);
+
 /* Peer recovery (replaces the gloo broadcast of shm bytes in
  * FullCkptReplicaManager.gather, REPL:275-332): the packed image is already
  * in device memory (received by NCCL broadcast from a surviving replica, or

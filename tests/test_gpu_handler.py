@@ -159,3 +159,38 @@ def test_ddp_checkpointer_gpu_roundtrip_and_async():
             AsyncCheckpointSaver._saver_instance.close()
             AsyncCheckpointSaver._saver_instance = None
         clear_sock_dir()
+
+
+def test_cold_restore_of_unpinned_segment_uses_bounce_ring():
+    """A restarted trainer attaches to a segment it has not pinned: the image
+    is streamed through the pinned ring (no cudaHostRegister on the critical
+    path), verified and unpacked; the segment is pinned in the background."""
+    torch.manual_seed(21)
+    tensors = {"w%d" % i: torch.randn(1 << 20, device="cuda") for i in range(40)}  # 160 MiB
+    tensors["odd"] = torch.randn(12345, device="cuda").to(torch.bfloat16)
+    sd = dict(tensors)
+    sd["step"] = 4
+    sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=4, paths={})
+    writer = SharedMemoryHandler(43, host=True)
+    try:
+        writer.save_state_dict(sd)
+        writer._drop_engine()  # as if the writing process were gone
+        reader = SharedMemoryHandler(43, host=False)
+        into = {k: torch.zeros_like(v) for k, v in tensors.items()}
+        into["step"] = 0
+        out = reader.load_state_dict(into=into)
+        assert reader.last_stats["restore_path"] == "bounced"
+        assert out["step"] == 4
+        for k, v in tensors.items():
+            assert torch.equal(into[k], v), k
+        # second restore in the same process: pinned by now
+        reader.load_state_dict(into=into)
+        assert reader.last_stats["restore_path"] == "registered"
+        reader._drop_engine()
+        writer.shared_memory.buf[5 << 20] ^= 0x01
+        with pytest.raises(_native.ChecksumMismatch):
+            reader.load_state_dict(into=into)
+        reader.close()
+    finally:
+        writer.unlink()
+        writer.close()
