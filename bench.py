@@ -36,6 +36,78 @@ WORKLOADS = {
     "gpt2-xl-1.5B-adamw-fp32": dict(n_layer=48, n_embd=1600, vocab=50304, block=128),
     "gpt2-small-124M-adamw-fp32": dict(n_layer=12, n_embd=768, vocab=50304, block=128),
 }
+# sharded workloads (configs 3 and 4 of BASELINE.json): per-rank shard fixed at
+# the 8-way size whatever --gpus is
+SHARDED = {
+    # Llama-2 7B, FSDP over 8 ranks: bf16 param shard + fp32 master / exp_avg /
+    # exp_avg_sq + step per tensor  (11.8 GB per rank)
+    "llama2-7b-fsdp8-shard": dict(kind="llama", layers=32, hidden=4096, inter=11008,
+                                  vocab=32000, ways=8),
+    # Megatron GPT 13B, TP=8: fp16 model shard + fp32 master / exp_avg /
+    # exp_avg_sq, CPU rng states  (~22.5 GB per rank)
+    "gpt-13b-tp8-shard": dict(kind="megatron", layers=40, hidden=5120, vocab=50304, ways=8),
+}
+
+
+def sharded_shapes(workload):
+    c = SHARDED[workload]
+    h, w = c["hidden"], c["ways"]
+    out = []
+    if c["kind"] == "llama":
+        out.append(("model.embed_tokens.weight", c["vocab"] * h))
+        for i in range(c["layers"]):
+            p = "model.layers.%d." % i
+            for n in ("self_attn.q_proj", "self_attn.k_proj", "self_attn.v_proj",
+                      "self_attn.o_proj"):
+                out.append((p + n + ".weight", h * h))
+            for n in ("mlp.gate_proj", "mlp.up_proj", "mlp.down_proj"):
+                out.append((p + n + ".weight", h * c["inter"]))
+            out.append((p + "input_layernorm.weight", h))
+            out.append((p + "post_attention_layernorm.weight", h))
+        out.append(("model.norm.weight", h))
+        out.append(("lm_head.weight", c["vocab"] * h))
+        return [(n, (numel + w - 1) // w) for n, numel in out]  # FSDP: 1/ways of each
+    # Megatron TP: matrices split w ways, layernorms / biases of row-parallel layers whole
+    out.append(("embedding.word_embeddings.weight", c["vocab"] * h // w))
+    out.append(("embedding.position_embeddings.weight", 2048 * h))
+    for i in range(c["layers"]):
+        p = "encoder.layers.%d." % i
+        out += [(p + "input_layernorm.weight", h), (p + "input_layernorm.bias", h),
+                (p + "self_attention.query_key_value.weight", 3 * h * h // w),
+                (p + "self_attention.query_key_value.bias", 3 * h // w),
+                (p + "self_attention.dense.weight", h * h // w),
+                (p + "self_attention.dense.bias", h),
+                (p + "post_attention_layernorm.weight", h),
+                (p + "post_attention_layernorm.bias", h),
+                (p + "mlp.dense_h_to_4h.weight", 4 * h * h // w),
+                (p + "mlp.dense_h_to_4h.bias", 4 * h // w),
+                (p + "mlp.dense_4h_to_h.weight", 4 * h * h // w),
+                (p + "mlp.dense_4h_to_h.bias", h)]
+    out += [("encoder.final_layernorm.weight", h), ("encoder.final_layernorm.bias", h)]
+    return out
+
+
+def build_sharded_state(workload, device, seed):
+    """Per-rank shard of configs 3 / 4 as the checkpointers hand it to the
+    engine: low-precision model shard + fp32 optimizer state (+ CPU rng
+    states for the Megatron one)."""
+    c = SHARDED[workload]
+    lowp = torch.bfloat16 if c["kind"] == "llama" else torch.float16
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    model, state = {}, {}
+    for idx, (name, numel) in enumerate(sharded_shapes(workload)):
+        master = torch.empty(numel, dtype=torch.float32, device=device).normal_(0, 0.02, generator=g)
+        model[name] = master.to(lowp)
+        state[idx] = {"step": torch.tensor(float(idx), device=device), "master": master,
+                      "exp_avg": torch.empty_like(master).normal_(0, 1e-3, generator=g),
+                      "exp_avg_sq": torch.empty_like(master).uniform_(0, 1e-6, generator=g)}
+    sd = {"model": model, "optimizer": {"state": state}, "iteration": 1000}
+    if c["kind"] == "megatron":
+        sd["rng_state"] = [{"torch_rng_state": torch.get_rng_state(),
+                            "cuda_rng_state": torch.cuda.get_rng_state(device)
+                            if torch.device(device).type == "cuda" else torch.get_rng_state()}]
+    return sd
 
 
 def gpt2_param_shapes(n_layer, n_embd, vocab, block):
@@ -54,6 +126,8 @@ def build_state(workload, device, seed, max_bytes=None):
     """{"model", "optimizer", "step"} as examples/pytorch/nanogpt/train.py:377-394
     builds it; synthetic random-init values.  `max_bytes` truncates the layer
     list (used for the bounded CPU-baseline sample)."""
+    if workload in SHARDED:
+        return build_sharded_state(workload, device, seed)
     cfg = WORKLOADS[workload]
     g = torch.Generator(device=device)
     g.manual_seed(seed)
@@ -88,6 +162,10 @@ def build_state(workload, device, seed, max_bytes=None):
 
 def workload_bytes(workload):
     """Payload bytes of the full state, from the shapes alone."""
+    if workload in SHARDED:
+        lowp = 2
+        tensors = sum(n * (lowp + 12) + 4 for _, n in sharded_shapes(workload))
+        return tensors + (5056 + 16 if SHARDED[workload]["kind"] == "megatron" else 0)
     total = 0
     for name, shape in gpt2_param_shapes(**WORKLOADS[workload]):
         n = int(np.prod(shape))
@@ -325,7 +403,7 @@ def run_ours(args, rank, local_rank, world):
         B = workload_bytes(workload)
 
     sd = build_state(workload, device, 1234 + rank)
-    assert state_bytes(sd) == B
+    B = state_bytes(sd)
     n_tensors = sum(1 for _ in _iter_tensors(sd))
 
     ckpt_dir = os.path.join(tempfile.gettempdir(), "fcpbench_%s" % os.environ["TORCHELASTIC_RUN_ID"])
@@ -365,18 +443,20 @@ def run_ours(args, rank, local_rank, world):
                     "chunk %d CRC differs from oracle" % c
                 parity["chunks_checked"] += 1
         del shm
-    snap_names = ["transformer.wpe.weight", "transformer.ln_f.weight",
-                  "transformer.h.0.attn.c_proj.weight"]
-    snaps = {n: sd["model"][n].clone() for n in snap_names if n in sd["model"]}
+    names = list(sd["model"].keys())
+    snap_names = [names[1], names[len(names) // 2], names[-2]]
+    snaps = {n: sd["model"][n].clone() for n in snap_names}
+    avg1 = sd["optimizer"]["state"][1]["exp_avg"].clone()
     for n in snaps:
         sd["model"][n].zero_()
     sd["optimizer"]["state"][1]["exp_avg"].add_(1.0)
-    ref_avg = None
     ckpt.load_checkpoint(into=sd)
     for n, s in snaps.items():
         assert torch.equal(sd["model"][n], s), "restore mismatch in %s" % n
         parity["tensors_checked"] += 1
-    del snaps, ref_avg
+    assert torch.equal(sd["optimizer"]["state"][1]["exp_avg"], avg1)
+    parity["tensors_checked"] += 1
+    del snaps, avg1
 
     # ---- native handles for the device-timed leg
     eng = handler._engine
@@ -443,6 +523,11 @@ def run_ours(args, rank, local_rank, world):
     torch.cuda.synchronize(device)
     restore_cold_s = _dist_max(time.perf_counter() - t0, device)
     cold_path = fresh.last_stats.get("restore_path")
+    cold_device_ms = fresh.last_stats.get("total_ms")
+    cold_breakdown = {k: fresh.last_stats.get(k) for k in
+                      ("restore_prepare_s", "restore_move_s", "restore_host_leaves_s")}
+    cold_breakdown["attach_and_meta_s"] = restore_cold_s - sum(
+        v or 0 for v in cold_breakdown.values())
     fresh.close()
     _barrier_sync(device)
 
@@ -459,11 +544,12 @@ def run_ours(args, rank, local_rank, world):
     # pageable copy_ loop (oracle port) fed with CUDA tensors, on a prefix of
     # the very same state dict
     ref_gpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    gpt2 = workload in WORKLOADS
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and gpt2:
         ref_gpu = reference_loop_on_gpu_tensors(sd, int(args.cpu_sample_gb * GB))
 
     cpu_base = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and gpt2:
         gbs, dt, sample, threads = cpu_reference_steps(workload, 3, 1, int(args.cpu_sample_gb * GB))
         cpu_base = {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port",
                     "sample": sample, "s_per_step": dt}
@@ -487,6 +573,8 @@ def run_ours(args, rank, local_rank, world):
             "save_durable_s": save_durable_ms / 1e3,
             "restore_s": restore_med_ms / 1e3,
             "restore_cold_s": restore_cold_s, "restore_cold_path": cold_path,
+            "restore_cold_copy_and_scatter_s": (cold_device_ms or 0) / 1e3,
+            "restore_cold_breakdown": cold_breakdown,
             "restore_cold_GBps_per_rank": B / restore_cold_s / GB,
             "save_GBps_per_rank": B / (save_durable_ms / 1e3) / GB,
             "restore_GBps_per_rank": B / (restore_med_ms / 1e3) / GB,
@@ -536,7 +624,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="gpt2-xl-1.5B-adamw-fp32", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="gpt2-xl-1.5B-adamw-fp32", choices=sorted(WORKLOADS) + sorted(SHARDED))
     ap.add_argument("--cpu-sample-gb", type=float, default=4.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

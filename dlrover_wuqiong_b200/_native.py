@@ -50,6 +50,7 @@ SYMBOLS = [
     ("fcp_restore_from_device", _i, [_vp, _vp, _i, _vp, _vp]),
     ("fcp_plan_timings", _i, [_vp, _vp]),
     ("fcp_plan_last_launches", _u64, [_vp]),
+    ("fcp_plan_set_copy_piece_bytes", _i, [_vp, _u64]),
     ("fcp_plan_set_slice_bytes", _i, [_vp, _u64]),
 ]
 
@@ -184,6 +185,9 @@ class Plan:
         out = (ctypes.c_float * 3)()
         check(lib().fcp_plan_timings(self._h, out))
         return {"kernel_ms": out[0], "copy_ms": out[1], "total_ms": out[2]}
+
+    def set_copy_piece_bytes(self, n):
+        check(lib().fcp_plan_set_copy_piece_bytes(self._h, n))
 
     def last_launches(self):
         return int(lib().fcp_plan_last_launches(self._h))

@@ -183,6 +183,7 @@ struct fcp_plan {
   uint64_t n_chunks = 0;
   uint64_t slice_bytes = 256ull << 20;  // smallest slice; they grow x2 up to x16
   uint64_t last_launches = 0;
+  uint64_t copy_piece = 0;  // split host copies at multiples of this (0 = never)
   std::vector<fcp_desc> h_descs;
   fcp_desc* d_descs = nullptr;
   uint32_t* d_region_sums = nullptr;
@@ -250,6 +251,26 @@ int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
                              rpc, cb, ce, st);
     if (rc) return rc;
     p->last_launches++;
+  }
+  return 0;
+}
+
+// Host<->device copy of image bytes [b0, b1).  When the host range was pinned
+// piece by piece (fcp_plan_set_copy_piece_bytes) no copy may straddle a piece
+// boundary: CUDA rejects a transfer that spans two registrations.
+int copy_image_range(fcp_plan* p, uint8_t* dev, uint8_t* host, uint64_t b0,
+                     uint64_t b1, bool to_host, cudaStream_t st) {
+  while (b0 < b1) {
+    uint64_t e = b1;
+    if (p->copy_piece) {
+      const uint64_t next = (b0 / p->copy_piece + 1) * p->copy_piece;
+      if (next < e) e = next;
+    }
+    if (to_host)
+      FCP_CUDA(cudaMemcpyAsync(host + b0, dev + b0, e - b0, cudaMemcpyDeviceToHost, st));
+    else
+      FCP_CUDA(cudaMemcpyAsync(dev + b0, host + b0, e - b0, cudaMemcpyHostToDevice, st));
+    b0 = e;
   }
   return 0;
 }
@@ -414,6 +435,12 @@ int fcp_plan_set_slice_bytes(fcp_plan* p, uint64_t slice_bytes) {
   return 0;
 }
 
+int fcp_plan_set_copy_piece_bytes(fcp_plan* p, uint64_t piece_bytes) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  p->copy_piece = piece_bytes;
+  return 0;
+}
+
 int fcp_host_register(void* base, uint64_t bytes, void** dev_alias) {
   if (!base || bytes == 0) return fail(-EINVAL, "empty host range");
   cudaError_t e = cudaHostRegister(
@@ -570,9 +597,10 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
       uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
       if (b1 > p->total) b1 = p->total;
       FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_slice[s], 0));
-      FCP_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(host_dst) + b0,
-                               static_cast<uint8_t*>(staging) + b0, b1 - b0,
-                               cudaMemcpyDeviceToHost, p->copy_stream));
+      rc = copy_image_range(p, static_cast<uint8_t*>(staging),
+                            static_cast<uint8_t*>(host_dst), b0, b1, true,
+                            p->copy_stream);
+      if (rc) return rc;
     }
     if (checksum && p->n_chunks) {
       rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
@@ -663,9 +691,10 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
       const uint64_t b0 = cb * p->chunk_bytes;
       uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
       if (b1 > p->total) b1 = p->total;
-      FCP_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(staging) + b0,
-                               static_cast<const uint8_t*>(host_src) + b0,
-                               b1 - b0, cudaMemcpyHostToDevice, p->copy_stream));
+      rc = copy_image_range(p, static_cast<uint8_t*>(staging),
+                            const_cast<uint8_t*>(static_cast<const uint8_t*>(host_src)),
+                            b0, b1, false, p->copy_stream);
+      if (rc) return rc;
       FCP_CUDA(cudaEventRecord(p->ev_slice[s], p->copy_stream));
       FCP_CUDA(cudaStreamWaitEvent(st, p->ev_slice[s], 0));
       rc = plan_launch(p, staging, 1, checksum, cb, ce, st, false);
@@ -735,7 +764,7 @@ int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
   if (n_workers > 32) n_workers = 32;
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
-  const uint64_t slot = 32ull << 20;
+  const uint64_t slot = 8ull << 20;  // small ring: pinned allocation costs ~0.5 s/GiB
   if (!p->ring || p->ring_workers < n_workers || p->ring_slot_bytes != slot) {
     if (p->ring) cudaFreeHost(p->ring);
     p->ring = nullptr;

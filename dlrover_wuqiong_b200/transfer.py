@@ -31,22 +31,45 @@ def buffer_address(buf):
     return ctypes.addressof(ctypes.c_char.from_buffer(buf))
 
 
-class HostMapping(object):
-    """cudaHostRegister'ed view of the shm segment (page-rounded)."""
+REGISTER_PIECE_BYTES = 64 << 20
 
-    def __init__(self, buf, nbytes):
+
+class HostMapping(object):
+    """cudaHostRegister'ed view of the shm segment.
+
+    Staged mode pins the segment in pieces of REGISTER_PIECE_BYTES: pinning is
+    serial inside the driver (~12 GB/s) and blocks other CUDA calls of the
+    process while it runs, so a restarted trainer pins in the background, one
+    piece at a time with a pause in between, and its training steps only ever
+    wait for one piece.  Direct mode needs one registration for the kernel's
+    alias and pins everything at once."""
+
+    def __init__(self, buf, nbytes, piece_bytes=REGISTER_PIECE_BYTES):
         self.addr = buffer_address(buf)
         self.nbytes = nbytes
+        self.piece = piece_bytes
+        self._done = []
+        self.register_s = 0.0
+        self.complete = False
+
+    def register_all(self, pause=0.0):
         t0 = time.time()
-        _native.host_register(self.addr, nbytes)
+        step = self.piece if self.piece else max(self.nbytes, 1)
+        for off in range(0, self.nbytes, step):
+            _native.host_register(self.addr + off, min(step, self.nbytes - off))
+            self._done.append(off)
+            if pause:
+                time.sleep(pause)
         self.register_s = time.time() - t0
-        self.alive = True
+        self.complete = True
+        return self
 
     def close(self):
-        if self.alive:
-            self.alive = False
+        done, self._done = self._done, []
+        self.complete = False
+        for off in done:
             try:
-                _native.host_unregister(self.addr)
+                _native.host_unregister(self.addr + off)
             except Exception as e:  # noqa: BLE001
                 logger.warning("host_unregister failed: %s", e)
 
@@ -157,27 +180,37 @@ class DeviceShardEngine(object):
     def _register_in_background(self, buf, total):
         """Pin the segment off the critical path (a restarted trainer's first
         save would otherwise pay ~0.08 s/GB for it)."""
+        mapping = HostMapping(buf, total, self._piece_bytes())
+
         def run():
             try:
                 with torch.cuda.device(self.device):
-                    self._mapping = HostMapping(buf, total)
-                    self.stats["register_s"] = self._mapping.register_s
+                    mapping.register_all(pause=0.002)
+                self._mapping = mapping
+                self.stats["register_s"] = mapping.register_s
             except Exception as e:  # noqa: BLE001 - retried synchronously by the next save
+                mapping.close()
                 logger.warning("background registration of the shm failed: %s", e)
 
         self._mapping_job = threading.Thread(target=run, name="fcp-register", daemon=True)
         self._mapping_job.start()
 
+    def _piece_bytes(self):
+        return 0 if self.mode == _native.MODE_DIRECT else REGISTER_PIECE_BYTES
+
     def _ensure_mapping(self, buf, total):
         self._join_mapping_job()
         addr = buffer_address(buf)
         if self._mapping is not None and (self._mapping.addr != addr
-                                          or self._mapping.nbytes < total):
+                                          or self._mapping.nbytes < total
+                                          or not self._mapping.complete):
             self._mapping.close()
             self._mapping = None
         if self._mapping is None and total:
-            self._mapping = HostMapping(buf, total)
+            self._mapping = HostMapping(buf, total, self._piece_bytes()).register_all()
             self.stats["register_s"] = self._mapping.register_s
+        if self._plan is not None:
+            self._plan.set_copy_piece_bytes(self._piece_bytes())
         return addr
 
     # -- save -------------------------------------------------------------
@@ -213,12 +246,15 @@ class DeviceShardEngine(object):
             for lf in leaves:
                 if lf.is_cuda and lf.nbytes and not lf.tensor.is_contiguous():
                     raise ValueError("restore target must be contiguous")
+            t_begin = time.perf_counter()
             ptrs, offs, sizes, host = self._sources(leaves)
             plan = self._ensure_plan(ptrs, offs, sizes, total)
             stream = torch.cuda.current_stream(self.device)
             staging_ptr = self._staging.data_ptr() if self._staging is not None else None
             checksum = self.checksum if expected is not None else _native.SUM_NONE
             self._join_mapping_job()
+            pin_later = False
+            t_ready = time.perf_counter()
             cold = (self._mapping is None or self._mapping.addr != buffer_address(buf)
                     or self._mapping.nbytes < total)
             if (cold and total and self.mode == _native.MODE_STAGED
@@ -232,14 +268,20 @@ class DeviceShardEngine(object):
                                      int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
                                      stream.cuda_stream)
                 self.stats["restore_path"] = "bounced"
-                self._register_in_background(buf, total)
+                pin_later = True
             else:
                 addr = self._ensure_mapping(buf, total)
                 plan.restore(addr, staging_ptr, self.mode, checksum, expected,
                              stream.cuda_stream)
                 self.stats["restore_path"] = "registered"
+            t_moved = time.perf_counter()
             self._stage_host_leaves(host, to_device=False)
+            if pin_later:
+                self._register_in_background(buf, total)
             self.stats.update(self._plan.timings())
+            self.stats["restore_prepare_s"] = t_ready - t_begin
+            self.stats["restore_move_s"] = t_moved - t_ready
+            self.stats["restore_host_leaves_s"] = time.perf_counter() - t_moved
 
     def restore_from_device(self, leaves, total, packed, expected=None):
         """Same, but the packed image is a device uint8 tensor (peer recovery)."""

@@ -203,7 +203,7 @@ int fcp_restore(fcp_plan* plan, const void* host_src, void* staging, int mode,
  * registered — the situation of a freshly restarted trainer attaching to the
  * shm segment its predecessor left (SAVER:305-306).  Pinning 19 GB takes
  * ~1.6 s (cudaHostRegister does not parallelise), so instead `n_workers` host
- * threads (<= 0: pick from the core count) copy 32 MiB slices of the image
+ * threads (<= 0: pick from the core count) copy 8 MiB slices of the image
  * into a small pinned ring owned by the plan and DMA them from there;
  * the scatter kernel then verifies and unpacks the staged image.
  * Synchronous.                                                              */
@@ -221,6 +221,12 @@ int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
 /* Device-side milliseconds of the phases of the last save / restore:
  * out[0] pack or scatter kernels, out[1] host-link copies, out[2] total.    */
 int fcp_plan_timings(fcp_plan* plan, float* out3);
+/* Tell the plan that the host image is pinned in separate pieces of
+ * `piece_bytes` (counted from its base): staged copies are then split so
+ * that none straddles two registrations (CUDA rejects those).  0 = one
+ * registration covers the image (default).  Direct mode needs the whole
+ * image in ONE registration.                                               */
+int fcp_plan_set_copy_piece_bytes(fcp_plan* plan, uint64_t piece_bytes);
 /* Number of kernels the last fcp_save_async / fcp_restore launched.          */
 uint64_t fcp_plan_last_launches(const fcp_plan* plan);
 /* Smallest slice of the staged pipelines (multiple of chunk_bytes; default
