@@ -81,6 +81,16 @@ __device__ __forceinline__ W8 load_packed(const uint8_t* packed, uint64_t o,
   return w;
 }
 
+// bytes [from, from+n) of w to consecutive addresses starting at t
+__device__ __noinline__ void store_some_bytes(uintptr_t t, const W8& w, int from,
+                                              int n) {
+#pragma unroll
+  for (int b = 0; b < kWordBytes; ++b)
+    if (b >= from && b < from + n)
+      reinterpret_cast<uint8_t*>(t)[b - from] =
+          static_cast<uint8_t>(w.v[b >> 2] >> ((b & 3) * 8));
+}
+
 // ---------------------------------------------------------------- the kernel
 // PACK = true : tensors -> packed image   (desc.ptr is the source)
 // PACK = false: packed image -> tensors   (desc.ptr is the target)
@@ -167,6 +177,48 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
             const W8 v = extract32(lo[k], hi[k], mis);
             st32(p0 + (row + k) * kRowBytes, v);
             if (CRC) acc = crc_word<REPL, RK>(tb, acc, v);
+          }
+        }
+      } else if (!PACK && mis != 0) {
+        // target not 32-byte aligned relative to the image: every lane writes
+        // the ALIGNED target word that starts inside its packed word, built
+        // from the tail of its own word and the head of its right neighbour's
+        // (one shuffle per register; lane 31 takes lane 0's word of the next
+        // row).  Only the few bytes at the very start and end of the region
+        // go out as byte stores.
+        const uint32_t keep = 32u - mis;        // bytes of my word before the aligned word
+        const uintptr_t tw = t0 + keep;         // my aligned target word, row 0
+        const uintptr_t src = reinterpret_cast<uintptr_t>(p0);
+#pragma unroll 1
+        for (int row = 0; row < kRows; row += kBatch) {
+          if (lane == 0 && row + kBatch < kRows)
+            prefetch_l2(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16);
+          W8 v[kBatch + 1];
+#pragma unroll
+          for (int k = 0; k < kBatch; ++k)
+            v[k] = ld32(reinterpret_cast<const void*>(src + (row + k) * kRowBytes));
+          const bool more = row + kBatch < kRows;
+          if (lane == 0 && more)  // first word of the next batch, for lane 31
+            v[kBatch] = ld32(reinterpret_cast<const void*>(src + (row + kBatch) * kRowBytes));
+#pragma unroll
+          for (int k = 0; k < kBatch; ++k) {
+            W8 hi;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t give = (lane == 0) ? v[k + 1].v[i] : v[k].v[i];
+              hi.v[i] = __shfl_sync(0xffffffffu, give, (lane + 1) & 31);
+            }
+            const bool last_row = !more && k == kBatch - 1;
+            if (row + k == 0 && lane == 0)
+              store_some_bytes(t0, v[k], 0, static_cast<int>(keep));
+            if (last_row && lane == 31) {
+              store_some_bytes(tw + (row + k) * kRowBytes, v[k], static_cast<int>(keep),
+                               static_cast<int>(mis));
+            } else {
+              st32(reinterpret_cast<void*>(tw + (row + k) * kRowBytes),
+                   extract32(v[k], hi, keep));
+            }
+            if (CRC) acc = crc_word<REPL, RK>(tb, acc, v[k]);
           }
         }
       } else {
