@@ -501,15 +501,26 @@ def run_ours(args, rank, local_rank, world):
 
     # ---- leg 3: training-blocking time of a save through the Python API
     block_s = []
+    prof = None
+    if os.getenv("FCP_PROFILE_BLOCKING") and rank == 0:
+        import cProfile
+        prof = cProfile.Profile()
     for k in range(K):
         wrapped = {"model_states": sd,
                    DLROVER_CKPT_CONFIG_KEY: CheckpointConfig(step=200 + k, paths={"model_states": path})}
         torch.cuda.synchronize(device)
         t0 = time.perf_counter()
+        if prof:
+            prof.enable()
         pending = handler.save_state_dict_async(wrapped)
         pending.wait_packed()
+        if prof:
+            prof.disable()
         block_s.append(time.perf_counter() - t0)
         pending.wait()
+    if prof:
+        import pstats
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(18)
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- leg 4: cold restore — what a restarted trainer sees: attach to the

@@ -272,16 +272,22 @@ class SharedMemoryHandler(object):
             conf = CheckpointConfig()
             meta_dict[DLROVER_CKPT_CONFIG_KEY] = conf
         conf.writing_shm = True
-        self.metadata.set(meta_dict)
         engine = self._engine_for(leaves)
+        if engine is not None and self.shared_memory is not None:
+            # GPU path: get the pack kernels going first, publish the
+            # "being rewritten" meta while they run.  The caller holds the shm
+            # lock for the whole save, so the agent cannot read in between;
+            # a trainer that dies in the ~2 ms window leaves the lock held
+            # (agent skips the shard) and a torn image fails its CRC.
+            engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf)
+            self.metadata.set(meta_dict)
+            return PendingSave(self, meta_dict, conf, engine)
+        self.metadata.set(meta_dict)
         if self.shared_memory is None:
             # nothing but empty tensors / scalars: the meta carries it all
             return PendingSave(self, meta_dict, conf, None)
-        if engine is not None:
-            engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf)
-        else:
-            _host_copy_leaves(leaves, self.shared_memory.buf)
-        return PendingSave(self, meta_dict, conf, engine)
+        _host_copy_leaves(leaves, self.shared_memory.buf)
+        return PendingSave(self, meta_dict, conf, None)
 
     def save_state_dict(self, state_dict):
         """Copy the state dict into the shm segment; complete on return

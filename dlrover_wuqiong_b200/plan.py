@@ -73,33 +73,40 @@ def collect_leaves(state_dict, meta_tree, refresh=True):
     on later saves, SAVER:174-194).  Returns None if the structure no longer
     matches."""
     leaves = []
+    Tensor = torch.Tensor
+
+    def is_container(x):
+        tx = type(x)
+        return tx is dict or tx is list or isinstance(x, (Mapping, list))
 
     def walk(v, m):
-        if isinstance(v, Mapping):
-            if not isinstance(m, dict):
+        # exact-type tests first: the abc isinstance() checks dominate the
+        # walk of a 1000-tensor dict otherwise
+        tv = type(v)
+        if tv is dict or (tv is not list and isinstance(v, Mapping)):
+            if type(m) is not dict:
                 return False
             for k, x in v.items():
-                if isinstance(x, (Mapping, list)) or torch.is_tensor(x):
+                if isinstance(x, Tensor) or is_container(x):
                     if k not in m or not walk(x, m[k]):
                         return False
                 elif refresh:
                     m[k] = x
             return True
-        if isinstance(v, list):
-            if not isinstance(m, list) or len(m) != len(v):
+        if tv is list or isinstance(v, list):
+            if type(m) is not list or len(m) != len(v):
                 return False
             for i, x in enumerate(v):
-                if isinstance(x, (Mapping, list)) or torch.is_tensor(x):
+                if isinstance(x, Tensor) or is_container(x):
                     if not walk(x, m[i]):
                         return False
                 elif refresh:
                     m[i] = x
             return True
         # tensor leaf
-        if not isinstance(m, TensorMeta):
+        if type(m) is not TensorMeta:
             return False
-        if (m.numel != v.numel() or m.dtype != v.dtype
-                or tuple(m.shape) != tuple(v.shape)):
+        if m.numel != v.numel() or m.dtype != v.dtype or m.shape != v.shape:
             return False
         leaves.append(Leaf(v, m))
         return True
