@@ -36,6 +36,10 @@ SYMBOLS = [
     ("fcp_plan_num_regions", _u64, [_vp]),
     ("fcp_host_register", _i, [_vp, _u64, ctypes.POINTER(_vp)]),
     ("fcp_host_unregister", _i, [_vp]),
+    ("fcp_enable_peer", _i, [_i, _i]),
+    ("fcp_ipc_export", _i, [_vp, _vp, _vp]),
+    ("fcp_ipc_open", _i, [_vp, ctypes.POINTER(_vp)]),
+    ("fcp_ipc_close", _i, [_vp]),
     ("fcp_pack", _i, [_vp, _vp, _i, _vp]),
     ("fcp_scatter", _i, [_vp, _vp, _i, _vp]),
     ("fcp_read_checksums", _i, [_vp, _vp, _vp]),
@@ -51,6 +55,7 @@ SYMBOLS = [
     ("fcp_plan_timings", _i, [_vp, _vp]),
     ("fcp_plan_last_launches", _u64, [_vp]),
     ("fcp_plan_set_copy_piece_bytes", _i, [_vp, _u64]),
+    ("fcp_plan_set_read_prefetch", _i, [_vp, _i]),
     ("fcp_plan_set_slice_bytes", _i, [_vp, _u64]),
 ]
 
@@ -189,6 +194,9 @@ class Plan:
     def set_copy_piece_bytes(self, n):
         check(lib().fcp_plan_set_copy_piece_bytes(self._h, n))
 
+    def set_read_prefetch(self, enable):
+        check(lib().fcp_plan_set_read_prefetch(self._h, 1 if enable else 0))
+
     def last_launches(self):
         return int(lib().fcp_plan_last_launches(self._h))
 
@@ -208,6 +216,45 @@ def host_register(addr, nbytes):
     alias = ctypes.c_void_p()
     check(lib().fcp_host_register(addr, nbytes, ctypes.byref(alias)))
     return alias.value
+
+
+def ipc_export(dev_ptr):
+    """-> (handle bytes, offset of dev_ptr inside its allocation)"""
+    handle = (ctypes.c_uint8 * 64)()
+    offset = ctypes.c_uint64()
+    check(lib().fcp_ipc_export(dev_ptr, handle, ctypes.byref(offset)))
+    return bytes(handle), int(offset.value)
+
+
+def ipc_open(handle):
+    base = ctypes.c_void_p()
+    buf = (ctypes.c_uint8 * 64).from_buffer_copy(handle)
+    check(lib().fcp_ipc_open(buf, ctypes.byref(base)))
+    return base.value
+
+
+def ipc_close(base):
+    check(lib().fcp_ipc_close(base))
+
+
+class RawDeviceImage(object):
+    """A packed image known only by its device address (e.g. a peer's staging
+    buffer mapped with ipc_open); quacks like the uint8 tensor the restore
+    paths expect."""
+    is_cuda = True
+
+    def __init__(self, ptr, nbytes):
+        self._ptr, self._n = ptr, nbytes
+
+    def data_ptr(self):
+        return self._ptr
+
+    def numel(self):
+        return self._n
+
+
+def enable_peer(device, peer):
+    check(lib().fcp_enable_peer(device, peer))
 
 
 def host_unregister(addr):

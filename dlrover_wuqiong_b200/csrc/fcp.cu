@@ -104,6 +104,8 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
   // longest run that still leaves every warp of a full grid >= 4 visits
   uint64_t run = regions / (static_cast<uint64_t>(sms) * 32 * 4);
   a.run = static_cast<uint32_t>(run < 1 ? 1 : run > fcpk::kMaxRun ? fcpk::kMaxRun : run);
+  static const bool no_pf = getenv("FCP_DEBUG_NO_PREFETCH") != nullptr;  // tuning aid
+  if (no_pf) a.flags |= fcpk::kNoPrefetch;
   // Big shape: one 1024-thread CTA per SM with the conflict-free (32x
   // replicated) update table and a 16x replicated row-shift table (212 KiB of
   // shared memory).  Small shape for images too small to give every warp of
@@ -184,6 +186,7 @@ struct fcp_plan {
   uint64_t slice_bytes = 256ull << 20;  // smallest slice; they grow x2 up to x16
   uint64_t last_launches = 0;
   uint64_t copy_piece = 0;  // split host copies at multiples of this (0 = never)
+  uint32_t kernel_flags = 0;
   std::vector<fcp_desc> h_descs;
   fcp_desc* d_descs = nullptr;
   uint32_t* d_region_sums = nullptr;
@@ -230,6 +233,8 @@ fcpk::Args plan_args(const fcp_plan* p, void* packed, uint64_t rb, uint64_t re) 
   a.region_end = re;
   a.packed = static_cast<uint8_t*>(packed);
   a.region_sums = p->d_region_sums;
+  a.run = 1;
+  a.flags = p->kernel_flags;
   return a;
 }
 
@@ -435,6 +440,13 @@ int fcp_plan_set_slice_bytes(fcp_plan* p, uint64_t slice_bytes) {
   return 0;
 }
 
+int fcp_plan_set_read_prefetch(fcp_plan* p, int enable) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (enable) p->kernel_flags &= ~fcpk::kNoPrefetch;
+  else p->kernel_flags |= fcpk::kNoPrefetch;
+  return 0;
+}
+
 int fcp_plan_set_copy_piece_bytes(fcp_plan* p, uint64_t piece_bytes) {
   if (!p) return fail(-EINVAL, "plan is NULL");
   p->copy_piece = piece_bytes;
@@ -461,6 +473,74 @@ int fcp_host_register(void* base, uint64_t bytes, void** dev_alias) {
     }
     *dev_alias = d;
   }
+  return 0;
+}
+
+int fcp_enable_peer(int device, int peer) {
+  if (device == peer) return 0;
+  DeviceGuard g(device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", device);
+  int can = 0;
+  FCP_CUDA(cudaDeviceCanAccessPeer(&can, device, peer));
+  if (!can) return fail(-ENOTSUP, "device %d cannot access device %d", device, peer);
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+  if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return fail(-EIO, "cudaDeviceEnablePeerAccess(%d) failed: %s", peer,
+                cudaGetErrorString(e));
+  }
+  cudaGetLastError();
+  return 0;
+}
+
+// ---- CUDA IPC of a device buffer (fused peer recovery) -------------------
+// cuMemGetAddressRange through the runtime's driver entry point lookup, so
+// the library needs no link-time dependency on libcuda.
+typedef int (*fcp_cuMemGetAddressRange_t)(unsigned long long*, size_t*, unsigned long long);
+
+static int allocation_base(const void* p, uintptr_t* base) {
+  static fcp_cuMemGetAddressRange_t fn = nullptr;
+  if (!fn) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuMemGetAddressRange", &sym, cudaEnableDefault, &q);
+    if (e != cudaSuccess || !sym) {
+      cudaGetLastError();
+      return fail(-ENOTSUP, "cuMemGetAddressRange is not available: %s", cudaGetErrorString(e));
+    }
+    fn = reinterpret_cast<fcp_cuMemGetAddressRange_t>(sym);
+  }
+  unsigned long long b = 0;
+  size_t n = 0;
+  const int rc = fn(&b, &n, reinterpret_cast<unsigned long long>(p));
+  if (rc != 0) return fail(-EIO, "cuMemGetAddressRange failed with %d", rc);
+  *base = static_cast<uintptr_t>(b);
+  return 0;
+}
+
+int fcp_ipc_export(const void* dev_ptr, uint8_t* handle64, uint64_t* offset) {
+  if (!dev_ptr || !handle64 || !offset) return fail(-EINVAL, "NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "unexpected IPC handle size");
+  uintptr_t base = 0;
+  int rc = allocation_base(dev_ptr, &base);
+  if (rc) return rc;
+  cudaIpcMemHandle_t h;
+  FCP_CUDA(cudaIpcGetMemHandle(&h, reinterpret_cast<void*>(base)));
+  memcpy(handle64, &h, 64);
+  *offset = reinterpret_cast<uintptr_t>(dev_ptr) - base;
+  return 0;
+}
+
+int fcp_ipc_open(const uint8_t* handle64, void** base) {
+  if (!handle64 || !base) return fail(-EINVAL, "NULL argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  FCP_CUDA(cudaIpcOpenMemHandle(base, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+int fcp_ipc_close(void* base) {
+  FCP_CUDA(cudaIpcCloseMemHandle(base));
   return 0;
 }
 
@@ -506,6 +586,8 @@ int fcp_launch(const fcp_desc* descs_dev, uint64_t n, uint64_t total_bytes,
   a.region_end = region_end;
   a.packed = static_cast<uint8_t*>(packed);
   a.region_sums = region_sums;
+  a.run = 1;
+  a.flags = 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   rc = launch_any(a, direction, checksum, dev, st);
   if (rc) return rc;
@@ -920,6 +1002,8 @@ extern "C" int fcp_launch_noalloc(const fcp_desc* descs_dev, uint64_t n,
   a.region_end = n_regions;
   a.packed = static_cast<uint8_t*>(packed);
   a.region_sums = scratch;
+  a.run = 1;
+  a.flags = 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   rc = launch_any(a, direction, checksum, dev, st);
   if (rc) return rc;

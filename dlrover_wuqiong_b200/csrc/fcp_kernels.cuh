@@ -266,7 +266,9 @@ struct Args {
   uint64_t region_begin, region_end;
   uint8_t* packed;
   uint32_t* region_sums;
-  uint32_t run;  // regions per warp visit, set by the launcher
+  uint32_t run;    // regions per warp visit, set by the launcher
+  uint32_t flags;  // kNoPrefetch: the read side is peer memory (never in local L2)
 };
+constexpr uint32_t kNoPrefetch = 1u;
 
 }  // namespace fcpk

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   const fcp_desc* __restrict__ descs = a.descs;
   const uint32_t n = a.n_desc;
   const uint64_t total = a.total;
+  const bool pf = (a.flags & kNoPrefetch) == 0;
 
   // A warp takes runs of a.run consecutive regions: the descriptor search is
   // paid once per run, inside a run the cursor just walks forward.
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
         const uintptr_t ta = t0 - mis;
 #pragma unroll 1
         for (int row = 0; row < kRows; row += 2) {
-          if (lane == 0 && row + 2 < kRows)
+          if (lane == 0 && pf && row + 2 < kRows)
             prefetch_l2(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 64);
           W8 lo[2], hi[2];
 #pragma unroll
@@ -191,7 +192,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
         const uintptr_t src = reinterpret_cast<uintptr_t>(p0);
 #pragma unroll 1
         for (int row = 0; row < kRows; row += kBatch) {
-          if (lane == 0 && row + kBatch < kRows)
+          if (lane == 0 && pf && row + kBatch < kRows)
             prefetch_l2(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16);
           W8 v[kBatch + 1];
 #pragma unroll
@@ -225,7 +226,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
         const uintptr_t src = PACK ? t0 : reinterpret_cast<uintptr_t>(p0);
 #pragma unroll 1
         for (int row = 0; row < kRows; row += kBatch) {
-          if (lane == 0 && row + kBatch < kRows)
+          if (lane == 0 && pf && row + kBatch < kRows)
             prefetch_l2(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16);
           W8 v[kBatch];
 #pragma unroll

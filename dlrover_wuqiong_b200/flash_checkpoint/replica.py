@@ -222,6 +222,56 @@ class FullCkptReplicaManager(CkptReplicaManger):
         dist.broadcast_object_list(metas, src=src_rank, group=self._backup_group)
         return payload, metas[0]
 
+    def recover_fused(self, shm_handler, into, group=None, healthy=True):
+        """Like recover_on_device, but without any collective on the data:
+        the survivor exports its staging image with CUDA IPC, every replaced
+        rank maps it and runs the scatter kernel straight on the PEER pointer,
+        so the bytes cross NVLink inside the kernel that verifies and unpacks
+        them (transfer fused with unpack; no receive buffer).  Same-node
+        ranks only.  Returns the restored step (0 if nobody had an image)."""
+        if not dist.is_initialized():
+            return 0
+        from .. import _native
+        engine = getattr(shm_handler, "_engine", None)
+        staging = engine.staging if (healthy and engine is not None) else None
+        meta = shm_handler.metadata.get(local=True) if healthy else {}
+        has_image = staging is not None and bool(meta) and FCP_CHECKSUM_KEY in meta
+        dev = torch.device("cuda", torch.cuda.current_device())
+        src_index = self._pick_source(
+            torch.tensor([1 if has_image else 0], dtype=torch.int8, device=dev), group)
+        if src_index is None:
+            return 0
+        src_rank = dist.get_global_rank(group, src_index) if group else src_index
+        me = dist.get_rank()
+        if me == src_rank:
+            torch.cuda.synchronize(dev)  # the image is complete
+            handle, offset = _native.ipc_export(staging.data_ptr())
+            box = [(meta, handle, offset, _meta_total_bytes(meta))]
+        else:
+            box = [None]
+        dist.broadcast_object_list(box, src=src_rank, group=group)
+        meta, handle, offset, total = box[0]
+        step = meta[DLROVER_CKPT_CONFIG_KEY].step
+        if me != src_rank:
+            import time
+            t0 = time.perf_counter()
+            with torch.cuda.device(dev):
+                base = _native.ipc_open(handle)  # the survivor's HBM, mapped here
+            t1 = time.perf_counter()
+            try:
+                shm_handler.restore_from_image(
+                    meta, _native.RawDeviceImage(base + offset, total), into)
+            finally:
+                torch.cuda.synchronize(dev)
+                t2 = time.perf_counter()
+                _native.ipc_close(base)
+            self.last_fused_stats = {"ipc_open_s": t1 - t0, "scatter_over_nvlink_s": t2 - t1,
+                                     "ipc_close_s": time.perf_counter() - t2, "bytes": total}
+            logger.info("rank %s restored step %s straight from the HBM of rank %s",
+                        me, step, src_rank)
+        dist.barrier(group=group)  # the survivor keeps the image alive until here
+        return step
+
     def recover_on_device(self, shm_handler, into, group=None, healthy=True):
         """Device transport: every rank of `group` (default: the main group,
         NCCL on GPU jobs) calls this with a state dict `into` of the

@@ -290,8 +290,13 @@ class DeviceShardEngine(object):
             plan = self._ensure_plan(ptrs, offs, sizes, total)
             stream = torch.cuda.current_stream(self.device)
             checksum = self.checksum if expected is not None else _native.SUM_NONE
-            plan.restore_from_device(packed.data_ptr(), checksum, expected,
-                                     stream.cuda_stream)
+            peer = isinstance(packed, _native.RawDeviceImage)  # a peer's HBM over NVLink
+            plan.set_read_prefetch(not peer)
+            try:
+                plan.restore_from_device(packed.data_ptr(), checksum, expected,
+                                         stream.cuda_stream)
+            finally:
+                plan.set_read_prefetch(True)
             self._stage_host_leaves(host, to_device=False)
 
     @property

@@ -218,6 +218,23 @@ int fcp_restore_bounced(fcp_plan* plan, const void* host_src, void* staging,
 int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
                             const uint32_t* expected, void* stream);
 
+/* Let kernels running on `device` dereference memory of `peer` (NVLink /
+ * NVSwitch P2P).  With it, fcp_restore_from_device can be given a pointer to
+ * the SURVIVING rank's staging image (mapped into this process with CUDA
+ * IPC): the scatter kernel then pulls the image over NVLink, verifies and
+ * unpacks it in one pass — transfer and unpack fused, no local copy of the
+ * image (replaces REPL:275-332 without even the NCCL broadcast).            */
+int fcp_enable_peer(int device, int peer);
+/* Export / map / unmap a device buffer between the processes of one node
+ * (CUDA IPC).  `dev_ptr` may point inside an allocation: the handle names the
+ * allocation, *offset is dev_ptr's distance from its base.  fcp_ipc_open is
+ * called with the receiving rank's device current and enables peer access to
+ * the owner lazily; every open must be paired with fcp_ipc_close before the
+ * owner frees the buffer.                                                   */
+int fcp_ipc_export(const void* dev_ptr, uint8_t* handle64, uint64_t* offset);
+int fcp_ipc_open(const uint8_t* handle64, void** base);
+int fcp_ipc_close(void* base);
+
 /* Device-side milliseconds of the phases of the last save / restore:
  * out[0] pack or scatter kernels, out[1] host-link copies, out[2] total.    */
 int fcp_plan_timings(fcp_plan* plan, float* out3);
@@ -227,6 +244,11 @@ int fcp_plan_timings(fcp_plan* plan, float* out3);
  * registration covers the image (default).  Direct mode needs the whole
  * image in ONE registration.                                               */
 int fcp_plan_set_copy_piece_bytes(fcp_plan* plan, uint64_t piece_bytes);
+/* The kernels pull the next batch of their read side into L2 with one bulk
+ * prefetch per warp.  Switch that off (enable = 0) when the read side is PEER
+ * memory: remote lines never live in the local L2, and the prefetch made the
+ * NVLink scatter 80x slower (6.7 -> 563 GB/s measured without it).          */
+int fcp_plan_set_read_prefetch(fcp_plan* plan, int enable);
 /* Number of kernels the last fcp_save_async / fcp_restore launched.          */
 uint64_t fcp_plan_last_launches(const fcp_plan* plan);
 /* Smallest slice of the staged pipelines (multiple of chunk_bytes; default

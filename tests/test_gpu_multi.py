@@ -86,6 +86,57 @@ def _worker(rank, world, port, run_id, tmpdir, errq):
         assert step == 11
         for k, v in rwant.items():
             assert torch.equal(rep.state_dict()[k], v), k
+        # --- same recovery, fused: the replaced rank's scatter kernel reads the
+        # survivor's staging image over NVLink (CUDA IPC), no receive buffer
+        if rank == 1:
+            with torch.no_grad():
+                for p in rep.parameters():
+                    p.fill_(-2.0)
+        step = mgr.recover_fused(handler, rsd, healthy=(rank == 0))
+        assert step == 11
+        for k, v in rwant.items():
+            assert torch.equal(rep.state_dict()[k], v), k
+
+        # --- rates on a 2 GiB replicated state (recorded, not asserted)
+        import json
+        import time
+        big = {"w%d" % i: torch.randn(64 << 20, device="cuda") for i in range(8)}  # 2 GiB
+        bwant = big["w3"][:1024].clone() if rank == 0 else None
+        bh = SharedMemoryHandler(20 + rank, host=True)
+        if rank == 0:
+            full = dict(big)
+            full[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=5, rank=0, world_size=world)
+            bh.save_state_dict(full)
+        rates = {}
+        for name, fn in (("nccl_broadcast_then_scatter", mgr.recover_on_device),
+                         ("fused_p2p_scatter", mgr.recover_fused)):
+            for it in range(3):
+                if rank == 1:
+                    big["w3"].zero_()
+                torch.cuda.synchronize()
+                dist.barrier()
+                t0 = time.perf_counter()
+                assert fn(bh, big, healthy=(rank == 0)) == 5
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+                rates[name] = min(rates.get(name, 1e9), dt)
+            ref = torch.empty(1024, device="cuda")
+            if rank == 0:
+                ref.copy_(bwant)
+            dist.broadcast(ref, src=0)
+            assert torch.equal(big["w3"][:1024], ref)
+        if rank == 1:
+            total = 8 * (64 << 20) * 4
+            out = {k: {"s": v, "GBps": total / v / 1e9} for k, v in rates.items()}
+            out["bytes"] = total
+            out["fused_breakdown"] = getattr(mgr, "last_fused_stats", None)
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", "peer_recovery.json"), "w") as f:
+                json.dump(out, f)
+        dist.barrier()
+        if rank == 0:
+            bh.unlink()
+        bh.close()
         dist.barrier()
         if rank == 0:
             handler.unlink()
@@ -112,7 +163,7 @@ def test_two_rank_nccl_save_restore_and_peer_recovery():
         for p in procs:
             p.start()
         for p in procs:
-            p.join(240)
+            p.join(150)
         alive = [p for p in procs if p.is_alive()]
         for p in alive:
             p.kill()
