@@ -183,7 +183,7 @@ struct fcp_plan {
   uint64_t n_desc = 0;
   uint64_t n_regions = 0;
   uint64_t n_chunks = 0;
-  uint64_t slice_bytes = 256ull << 20;  // smallest slice; they grow x2 up to x16
+  uint64_t slice_bytes = 1ull << 30;  // smallest slice; they grow x2 up to x4
   uint64_t last_launches = 0;
   uint64_t copy_piece = 0;  // split host copies at multiples of this (0 = never)
   uint32_t kernel_flags = 0;
@@ -281,7 +281,7 @@ int copy_image_range(fcp_plan* p, uint8_t* dev, uint8_t* host, uint64_t b0,
 }
 
 // Chunk ranges of the staged pipelines.  Sizes double from slice_bytes up to
-// 16x: a save starts its first DMA after a small pack and keeps the copy
+// 4x: a save starts its first DMA after a small pack and keeps the copy
 // engine busy behind ever larger (more efficient) kernels; a restore runs
 // the schedule backwards so only a small scatter trails the last DMA.
 std::vector<std::pair<uint64_t, uint64_t>> make_slices(const fcp_plan* p,
@@ -293,7 +293,7 @@ std::vector<std::pair<uint64_t, uint64_t>> make_slices(const fcp_plan* p,
     const uint64_t take = cur < left ? cur : left;
     sizes.push_back(take);
     left -= take;
-    if (cur < 16 * cps0) cur *= 2;
+    if (cur < 4 * cps0) cur *= 2;
   }
   if (!growing) std::reverse(sizes.begin(), sizes.end());
   std::vector<std::pair<uint64_t, uint64_t>> out;
