@@ -165,7 +165,7 @@ class PendingSave(object):
         else:
             self._meta.pop(FCP_CHECKSUM_KEY, None)
         self._conf.writing_shm = False
-        h.metadata.set(self._meta)
+        h._publish(self._meta, self._conf)
 
 
 class SharedMemoryHandler(object):
@@ -190,6 +190,8 @@ class SharedMemoryHandler(object):
         self._need_creation = True
         self._engine = None
         self._n_metas = -1
+        self._delta_ok = False  # the agent holds the meta tree of the current layout
+        self._changes = []      # non-tensor leaves refreshed by the current save
         self.last_stats = {}
 
     # -- lifecycle ----------------------------------------------------------
@@ -232,6 +234,34 @@ class SharedMemoryHandler(object):
         self._buffer_size += value.numel() * value.element_size()
         return meta
 
+    def _announce(self, meta_dict, conf):
+        """Tell the agent the image is being rewritten (writing_shm=True)."""
+        if self._delta_ok:
+            try:
+                if self.metadata.update([((DLROVER_CKPT_CONFIG_KEY,), conf)]):
+                    return
+            except Exception:  # noqa: BLE001
+                pass
+            self._delta_ok = False
+        self.metadata.set(meta_dict)
+
+    def _publish(self, meta_dict, conf):
+        """Make the agent's copy of the meta equal `meta_dict`: by paths when
+        it already holds this layout (config, checksums and the refreshed
+        non-tensor leaves are all that changed), else as a whole."""
+        if self._delta_ok:
+            updates = list(self._changes)
+            updates.append(((DLROVER_CKPT_CONFIG_KEY,), conf))
+            if FCP_CHECKSUM_KEY in meta_dict:
+                updates.append(((FCP_CHECKSUM_KEY,), meta_dict[FCP_CHECKSUM_KEY]))
+            try:
+                if self.metadata.update(updates):
+                    return
+            except Exception as e:  # noqa: BLE001 - fall back to the full set
+                logger.debug("meta update failed (%s); sending the whole meta", e)
+        self.metadata.set(meta_dict)
+        self._delta_ok = os.getenv("FCP_META_DELTA", "1") == "1"
+
     def _layout_for(self, state_dict):
         """(meta_dict, leaves) for this save: the cached layout if the dict
         still has the same structure, a fresh one (and a fresh segment of the
@@ -239,10 +269,13 @@ class SharedMemoryHandler(object):
         if self.shared_memory is not None:
             meta_dict = self.metadata.get(local=True)
             if meta_dict:
-                leaves = _plan.collect_leaves(state_dict, meta_dict)
+                self._changes = []
+                leaves = _plan.collect_leaves(state_dict, meta_dict, changes=self._changes)
                 if leaves is not None and len(leaves) == self._n_metas:
                     return meta_dict, leaves
                 logger.info("state dict structure changed; rebuilding the shm layout")
+        self._delta_ok = False  # new layout: the agent needs the whole tree
+        self._changes = []
         meta_dict, leaves, total = _plan.build_layout(state_dict)
         self._buffer_size = total
         self._n_metas = len(leaves)
@@ -280,9 +313,9 @@ class SharedMemoryHandler(object):
             # a trainer that dies in the ~2 ms window leaves the lock held
             # (agent skips the shard) and a torn image fails its CRC.
             engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf)
-            self.metadata.set(meta_dict)
+            self._announce(meta_dict, conf)
             return PendingSave(self, meta_dict, conf, engine)
-        self.metadata.set(meta_dict)
+        self._announce(meta_dict, conf)
         if self.shared_memory is None:
             # nothing but empty tensors / scalars: the meta carries it all
             return PendingSave(self, meta_dict, conf, None)
@@ -308,7 +341,7 @@ class SharedMemoryHandler(object):
         config = meta_dict.get(DLROVER_CKPT_CONFIG_KEY, CheckpointConfig())
         if not meta_dict or config.writing_shm:
             return {}
-        if self.shared_memory is None or self._need_creation:
+        if self.shared_memory is None or self._need_creation or self._segment_replaced():
             self.init_shared_memory(create=False)
         if not self.shared_memory:
             return {}
@@ -376,6 +409,14 @@ class SharedMemoryHandler(object):
                         lf.tensor.copy_(src.view(lf.meta.dtype).reshape(lf.meta.shape)
                                         if lf.meta.offset % lf.meta.element_size == 0
                                         else src.clone().view(lf.meta.dtype).reshape(lf.meta.shape))
+
+    def _segment_replaced(self):
+        """The writer re-creates the segment when the layout changes; a reader
+        still mapped to the old one must re-attach."""
+        try:
+            return os.stat("/dev/shm/" + self._shm_name).st_size != self.shared_memory.size
+        except OSError:
+            return False
 
     def no_checkpint_state(self):
         """True if no shard has ever been saved (handlers attach lazily, so

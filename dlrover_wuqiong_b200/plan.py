@@ -66,12 +66,13 @@ def build_layout(state_dict):
     return meta, leaves, total
 
 
-def collect_leaves(state_dict, meta_tree, refresh=True):
+def collect_leaves(state_dict, meta_tree, refresh=True, changes=None):
     """Pair the tensors of `state_dict` with the TensorMeta objects of an
     existing `meta_tree` of the same structure, refreshing non-tensor leaves in
     the tree on the way unless refresh=False (what _traverse_copy_to_shm does
     on later saves, SAVER:174-194).  Returns None if the structure no longer
-    matches."""
+    matches.  If `changes` is a list, every refreshed non-tensor leaf is also
+    appended to it as (path, value)."""
     leaves = []
     Tensor = torch.Tensor
 
@@ -79,7 +80,7 @@ def collect_leaves(state_dict, meta_tree, refresh=True):
         tx = type(x)
         return tx is dict or tx is list or isinstance(x, (Mapping, list))
 
-    def walk(v, m):
+    def walk(v, m, path=()):
         # exact-type tests first: the abc isinstance() checks dominate the
         # walk of a 1000-tensor dict otherwise
         tv = type(v)
@@ -88,20 +89,24 @@ def collect_leaves(state_dict, meta_tree, refresh=True):
                 return False
             for k, x in v.items():
                 if isinstance(x, Tensor) or is_container(x):
-                    if k not in m or not walk(x, m[k]):
+                    if k not in m or not walk(x, m[k], path + (k,)):
                         return False
                 elif refresh:
                     m[k] = x
+                    if changes is not None:
+                        changes.append((path + (k,), x))
             return True
         if tv is list or isinstance(v, list):
             if type(m) is not list or len(m) != len(v):
                 return False
             for i, x in enumerate(v):
                 if isinstance(x, Tensor) or is_container(x):
-                    if not walk(x, m[i]):
+                    if not walk(x, m[i], path + (i,)):
                         return False
                 elif refresh:
                     m[i] = x
+                    if changes is not None:
+                        changes.append((path + (i,), x))
             return True
         # tensor leaf
         if type(m) is not TensorMeta:

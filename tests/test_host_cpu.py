@@ -373,3 +373,50 @@ def test_saver_breakpoint_save_and_skip_when_locked(saver_env):
                                                global_shard_num=3))
         assert _wait_for(lambda: saver.global_shard_num == 3)
         ckpt.close()
+
+
+def test_meta_delta_updates_between_trainer_and_agent():
+    """Second and later saves of an unchanged layout send only config,
+    checksums and refreshed non-tensor leaves by path; the agent's copy must
+    still equal the trainer's, and a layout change falls back to a full set."""
+    agent = SharedMemoryHandler(34, host=True)     # serves the meta dict
+    trainer = SharedMemoryHandler(34, host=False)  # client, as in a training process
+    try:
+        sets = []
+        real_set = trainer.metadata.set
+        trainer.metadata.set = lambda d: (sets.append(1), real_set(d))[1]
+        model = SimpleNet()
+        opt = torch.optim.SGD(model.parameters(), lr=0.5)
+        sd = {"model": model.state_dict(), "optimizer": opt.state_dict(), "step": 1,
+              DLROVER_CKPT_CONFIG_KEY: CheckpointConfig(step=1, paths={"model_states": "/a"})}
+        trainer.save_state_dict(sd)
+        assert len(sets) == 2  # new layout: full meta, twice (writing, done)
+        opt.param_groups[0]["lr"] = 0.25
+        sd = {"model": model.state_dict(), "optimizer": opt.state_dict(), "step": 2,
+              DLROVER_CKPT_CONFIG_KEY: CheckpointConfig(step=2, paths={"model_states": "/b"})}
+        trainer.save_state_dict(sd)
+        assert len(sets) == 2  # nothing but path updates this time
+        served = agent.metadata.get()
+        assert served["step"] == 2
+        assert served[DLROVER_CKPT_CONFIG_KEY].step == 2
+        assert served[DLROVER_CKPT_CONFIG_KEY].paths == {"model_states": "/b"}
+        assert served[DLROVER_CKPT_CONFIG_KEY].writing_shm is False
+        assert served["optimizer"]["param_groups"][0]["lr"] == 0.25
+        assert served == trainer.metadata.get(local=True)
+        out = agent.load_state_dict()
+        assert out["step"] == 2 and torch.equal(out["model"]["fc1.weight"], model.fc1.weight)
+        # layout change -> full set again
+        sd["extra"] = torch.ones(3)
+        sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=3, paths={})
+        trainer.save_state_dict(sd)
+        assert len(sets) == 4
+        assert torch.equal(agent.load_state_dict()["extra"], torch.ones(3))
+        # agent restarted (empty dict): the update is refused, the full meta follows
+        agent.metadata._dict = {}
+        sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=4, paths={})
+        trainer.save_state_dict(sd)
+        assert agent.metadata.get()[DLROVER_CKPT_CONFIG_KEY].step == 4
+    finally:
+        trainer.close()
+        agent.unlink()
+        agent.close()
