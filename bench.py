@@ -29,6 +29,7 @@ import torch.distributed as dist  # noqa: E402
 
 GB = 1e9
 PCIE_GEN5_X16_GBS = 64.0
+_REAL_STDOUT = sys.stdout
 
 WORKLOADS = {
     # nanoGPT shapes, bias=False, block_size 128: fp32 params (tied
@@ -373,7 +374,7 @@ def run_reference_arm(args, rank, world):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "host": host_info(),
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
 def run_ours(args, rank, local_rank, world):
@@ -576,7 +577,7 @@ def run_ours(args, rank, local_rank, world):
             "config": {
                 "workload": workload, "shard_bytes_per_rank": B, "tensors_per_rank": n_tensors,
                 "step": "save HBM->shm (durable, CRC32C/2MiB) + restore shm->live tensors (verified)",
-                "transfer_mode": "staged" if mode == _native.MODE_STAGED else "direct",
+                "transfer_mode": {0: "staged", 1: "direct", 2: "staged_kernel"}[mode],
                 "l2": "inputs (%.1f GB) larger than L2" % (B / GB), "note": note,
                 "host_link_peak_GBps_per_dir": PCIE_GEN5_X16_GBS},
             "save_blocking_s": save_blocking_s,
@@ -604,7 +605,7 @@ def run_ours(args, rank, local_rank, world):
             "gpu_launches": launches,
             "clocks": clocks, "parity": parity, "host": hi,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
     ckpt.close()
     if dist.is_initialized():
@@ -639,6 +640,13 @@ def main():
     ap.add_argument("--cpu-sample-gb", type=float, default=4.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+
+    # keep stdout for the one JSON line: libraries (NCCL's version banner, ...)
+    # write to fd 1 behind Python's back, so point fd 1 at stderr meanwhile
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     rank = int(os.environ.get("RANK", 0))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))

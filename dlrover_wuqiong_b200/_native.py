@@ -17,7 +17,7 @@ REGION_BYTES = 16384
 NOALLOC_MAX_BYTES = 65536 * REGION_BYTES
 DEFAULT_CHUNK_BYTES = 2 << 20
 SUM_NONE, SUM_CRC32C = 0, 1
-MODE_STAGED, MODE_DIRECT = 0, 1
+MODE_STAGED, MODE_DIRECT, MODE_STAGED_KERNEL = 0, 1, 2
 
 # struct fcp_desc { const void* ptr; uint64_t dst_off; uint64_t nbytes; }
 DESC_DTYPE = np.dtype([("ptr", "<u8"), ("dst_off", "<u8"), ("nbytes", "<u8")])

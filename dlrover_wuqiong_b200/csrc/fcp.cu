@@ -649,9 +649,9 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
   if (!p) return fail(-EINVAL, "plan is NULL");
   if (p->save_in_flight) return fail(-EBUSY, "a save is already in flight");
   if (!host_dst && p->total) return fail(-EINVAL, "host_dst is NULL");
-  if (mode == FCP_MODE_STAGED && !staging && p->total)
-    return fail(-EINVAL, "staged mode needs a staging buffer");
-  if (mode != FCP_MODE_STAGED && mode != FCP_MODE_DIRECT)
+  if (mode != FCP_MODE_DIRECT && !staging && p->total)
+    return fail(-EINVAL, "staged modes need a staging buffer");
+  if (mode != FCP_MODE_STAGED && mode != FCP_MODE_DIRECT && mode != FCP_MODE_STAGED_KERNEL)
     return fail(-EINVAL, "bad mode %d", mode);
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
@@ -667,6 +667,16 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
     FCP_CUDA(cudaEventRecord(p->ev_packed, st));
     FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_packed, 0));
   } else {
+    uint8_t* host_alias = nullptr;
+    if (mode == FCP_MODE_STAGED_KERNEL && p->total) {
+      // every piece of the segment is registered as mapped; with unified
+      // addressing its device alias is the host address itself
+      void* a0 = nullptr;
+      FCP_CUDA(cudaHostGetDevicePointer(&a0, host_dst, 0));
+      if (a0 != host_dst)
+        return fail(-ENOTSUP, "host pointer is not usable from the device as is");
+      host_alias = static_cast<uint8_t*>(a0);
+    }
     const auto slices = make_slices(p, true);
     rc = plan_slice_events(p, slices.size());
     if (rc) return rc;
@@ -679,10 +689,19 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
       uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
       if (b1 > p->total) b1 = p->total;
       FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_slice[s], 0));
-      rc = copy_image_range(p, static_cast<uint8_t*>(staging),
-                            static_cast<uint8_t*>(host_dst), b0, b1, true,
-                            p->copy_stream);
-      if (rc) return rc;
+      if (mode == FCP_MODE_STAGED_KERNEL) {
+        static const int ctas = getenv("FCP_COPY_CTAS") ? atoi(getenv("FCP_COPY_CTAS")) : 32;
+        const uint64_t n = b1 - b0;  // b0 is a multiple of the chunk size
+        fcpk::fcp_copy_kernel<<<ctas > 0 ? ctas : 32, 256, 0, p->copy_stream>>>(
+            static_cast<const uint8_t*>(staging) + b0, host_alias + b0, n / 32, n % 32);
+        FCP_CUDA(cudaGetLastError());
+        p->last_launches++;
+      } else {
+        rc = copy_image_range(p, static_cast<uint8_t*>(staging),
+                              static_cast<uint8_t*>(host_dst), b0, b1, true,
+                              p->copy_stream);
+        if (rc) return rc;
+      }
     }
     if (checksum && p->n_chunks) {
       rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
@@ -747,6 +766,7 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
   if (!host_src && p->total) return fail(-EINVAL, "host_src is NULL");
   if (expected && !checksum)
     return fail(-EINVAL, "expected sums given but checksum disabled");
+  if (mode == FCP_MODE_STAGED_KERNEL) mode = FCP_MODE_STAGED;  // reads: copy engine
   if (mode == FCP_MODE_STAGED && !staging && p->total)
     return fail(-EINVAL, "staged mode needs a staging buffer");
   if (mode != FCP_MODE_STAGED && mode != FCP_MODE_DIRECT)

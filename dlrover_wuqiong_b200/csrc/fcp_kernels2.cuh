@@ -287,6 +287,27 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   }
 }
 
+// Plain streaming copy used by FCP_MODE_STAGED_KERNEL to move the staged
+// image into host-mapped memory with SM stores instead of the copy engine
+// (a few CTAs are enough to fill the host link, so it can run beside the next
+// training step).  Both pointers 32-byte aligned; n_words = bytes / 32.
+__global__ void __launch_bounds__(256) fcp_copy_kernel(const uint8_t* __restrict__ src,
+                                                       uint8_t* __restrict__ dst,
+                                                       uint64_t n_words, uint64_t tail_bytes) {
+  const uint64_t stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+  uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n_words; i += 4 * stride) {
+    W8 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = ld32_stream(src + (i + k * stride) * kWordBytes);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) st32(dst + (i + k * stride) * kWordBytes, v[k]);
+  }
+  for (; i < n_words; i += stride) st32(dst + i * kWordBytes, ld32_stream(src + i * kWordBytes));
+  if (blockIdx.x == 0 && threadIdx.x < tail_bytes)
+    dst[n_words * kWordBytes + threadIdx.x] = src[n_words * kWordBytes + threadIdx.x];
+}
+
 // One thread per chunk: Horner over the chunk's region values.  The value
 // written is the raw CRC of the chunk zero-padded to a whole number of
 // regions; the host strips the padding and applies init/xorout

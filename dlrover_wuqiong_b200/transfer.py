@@ -22,8 +22,12 @@ CHECKSUM_KEY = "_FCP_CHECKSUMS"  # extra top-level meta key (ignored by savers)
 
 
 def _mode_from_env():
-    return _native.MODE_DIRECT if os.getenv("FCP_TRANSFER_MODE", "staged") == "direct" \
-        else _native.MODE_STAGED
+    """FCP_TRANSFER_MODE = staged (copy engine, default) | staged_kernel (copy
+    kernel for the device->host leg) | direct (pack kernel writes the host
+    segment itself)."""
+    return {"direct": _native.MODE_DIRECT,
+            "staged_kernel": _native.MODE_STAGED_KERNEL}.get(
+                os.getenv("FCP_TRANSFER_MODE", "staged"), _native.MODE_STAGED)
 
 
 def buffer_address(buf):
@@ -165,7 +169,7 @@ class DeviceShardEngine(object):
         else:
             self._plan.update_ptrs(ptrs)
         need = self._plan.staging_bytes
-        if self.mode == _native.MODE_STAGED and (
+        if self.mode != _native.MODE_DIRECT and (
                 self._staging is None or self._staging.numel() < need):
             self._staging = None
             self._staging = torch.empty(need, dtype=torch.uint8, device=self.device)
@@ -257,7 +261,7 @@ class DeviceShardEngine(object):
             t_ready = time.perf_counter()
             cold = (self._mapping is None or self._mapping.addr != buffer_address(buf)
                     or self._mapping.nbytes < total)
-            if (cold and total and self.mode == _native.MODE_STAGED
+            if (cold and total and self.mode != _native.MODE_DIRECT
                     and os.getenv("FCP_COLD_RESTORE", "bounce") == "bounce"):
                 # fresh process, segment not pinned yet: stream it through the
                 # pinned ring now, pin it in the background for later saves

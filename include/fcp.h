@@ -51,6 +51,13 @@ extern "C" {
 /* transfer modes of fcp_save_async / fcp_restore */
 #define FCP_MODE_STAGED 0 /* kernel <-> HBM staging, copy engine <-> host   */
 #define FCP_MODE_DIRECT 1 /* kernel reads/writes host-mapped memory itself  */
+#define FCP_MODE_STAGED_KERNEL 2 /* save: pack into HBM staging (short blocking
+                                  * time, as STAGED), then a small copy KERNEL
+                                  * on the plan's side stream stores the image
+                                  * into the host-mapped segment; restore: as
+                                  * STAGED.  Kernel-issued host writes kept
+                                  * scaling across GPUs where copy-engine
+                                  * writes did not.             */
 
 /* One tensor of the state dict.  Replaces the (value, TensorMeta) pair that
  * _write_shared_memory / _read_tensor_from_buf receive (SAVER:197-206,
