@@ -397,7 +397,12 @@ def run_ours(args, rank, local_rank, world):
     need_host = world * B * 1.15 + (2.5 * args.cpu_sample_gb * GB if world == 1 else 0)
     free_hbm, _ = torch.cuda.mem_get_info(device)
     note = None
-    if need_host > 0.85 * avail or 2.3 * B > free_hbm:
+    try:
+        st = os.statvfs("/dev/shm")
+        shm_free = st.f_bavail * st.f_frsize
+    except OSError:
+        shm_free = avail
+    if need_host > 0.85 * avail or world * B * 1.05 > shm_free or 2.3 * B > free_hbm:
         note = "%s does not fit (host %.0f GB avail, HBM %.0f GB free)" % (
             workload, avail / GB, free_hbm / GB)
         workload = "gpt2-small-124M-adamw-fp32"

@@ -158,7 +158,8 @@ def _host_buffer(nbytes):
     return mm, arr
 
 
-@pytest.mark.parametrize("mode", [_native.MODE_STAGED, _native.MODE_DIRECT])
+@pytest.mark.parametrize("mode", [_native.MODE_STAGED, _native.MODE_DIRECT,
+                                  _native.MODE_STAGED_KERNEL])
 def test_save_restore_through_host_memory(mode):
     rng = np.random.default_rng(21)
     flat, total, expect = _random_case(rng, 200, 60000, DT, 0, True)
