@@ -45,6 +45,7 @@ SYMBOLS = [
     ("fcp_read_checksums", _i, [_vp, _vp, _vp]),
     ("fcp_launch", _i, [_vp, _u64, _u64, _u32, _u64, _u64, _vp, _vp, _vp, _i, _i, _vp]),
     ("fcp_finish_checksums", _i, [_vp, _u64, _u64, _u32, _vp]),
+    ("fcp_chunk_xxh64", _i, [_vp, _u64, _u32, _vp, _vp]),
     ("fcp_launch_noalloc", _i, [_vp, _u64, _u64, _u32, _vp, _vp, _i, _i, _vp]),
     ("fcp_save_async", _i, [_vp, _vp, _vp, _i, _i, _vp]),
     ("fcp_save_packed_wait", _i, [_vp]),
@@ -259,6 +260,11 @@ def enable_peer(device, peer):
 
 def host_unregister(addr):
     check(lib().fcp_host_unregister(addr))
+
+
+def chunk_xxh64(packed_ptr, total_bytes, out_ptr, chunk_bytes=DEFAULT_CHUNK_BYTES, stream=0):
+    """XXH64 of every chunk of a device-resident image into device memory."""
+    check(lib().fcp_chunk_xxh64(packed_ptr, total_bytes, chunk_bytes, out_ptr, stream))
 
 
 def finish_checksums(raw, total_bytes, chunk_bytes=DEFAULT_CHUNK_BYTES):

@@ -159,7 +159,7 @@ class PendingSave(object):
             if sums is not None:
                 from .transfer import checksums_to_meta
                 self._meta[FCP_CHECKSUM_KEY] = checksums_to_meta(
-                    sums, self._engine.chunk_bytes)
+                    sums, self._engine.chunk_bytes, self._engine.stats.get("xxh64"))
             else:
                 self._meta.pop(FCP_CHECKSUM_KEY, None)
         else:
@@ -367,9 +367,11 @@ class SharedMemoryHandler(object):
         engine = self._engine_for(leaves)
         if engine is not None:
             from .transfer import checksums_from_meta
-            expected = checksums_from_meta(meta_dict.get(FCP_CHECKSUM_KEY), total,
-                                           engine.chunk_bytes)
-            engine.restore(leaves, total, self.shared_memory.buf, expected)
+            entry = meta_dict.get(FCP_CHECKSUM_KEY)
+            expected = checksums_from_meta(entry, total, engine.chunk_bytes)
+            engine.restore(leaves, total, self.shared_memory.buf, expected,
+                           expected_xxh64=(entry or {}).get("xxh64") if expected is not None
+                           else None)
             self.last_stats = dict(engine.stats)
         else:
             for lf in leaves:

@@ -597,6 +597,24 @@ int fcp_launch(const fcp_desc* descs_dev, uint64_t n, uint64_t total_bytes,
   return rc;
 }
 
+int fcp_chunk_xxh64(const void* packed, uint64_t total_bytes, uint32_t chunk_bytes,
+                    uint64_t* out, void* stream) {
+  if (chunk_bytes == 0 || chunk_bytes % 32 != 0)
+    return fail(-EINVAL, "chunk_bytes %u is not a multiple of 32", chunk_bytes);
+  if (total_bytes == 0) return 0;
+  if (!packed || !out) return fail(-EINVAL, "NULL argument");
+  const uint64_t n_chunks = ceil_div(total_bytes, chunk_bytes);
+  const unsigned threads = 128;
+  const uint64_t blocks = ceil_div(n_chunks * 4, threads);
+  if (blocks > 0x7fffffffull) return fail(-E2BIG, "too many chunks");
+  fcpk::fcp_xxh64_kernel<<<static_cast<unsigned>(blocks), threads, 0,
+                           static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(packed), total_bytes, chunk_bytes, 0, n_chunks,
+      reinterpret_cast<unsigned long long*>(out));
+  FCP_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int fcp_finish_checksums(const uint32_t* raw, uint64_t n_chunks,
                          uint64_t total_bytes, uint32_t chunk_bytes,
                          uint32_t* out) {

@@ -308,6 +308,85 @@ __global__ void __launch_bounds__(256) fcp_copy_kernel(const uint8_t* __restrict
     dst[n_words * kWordBytes + threadIdx.x] = src[n_words * kWordBytes + threadIdx.x];
 }
 
+// ------------------------------------------------------------------ XXH64
+// Standard XXH64 (seed 0) of every chunk of a device-resident packed image.
+// The algorithm is four serial lanes per stream, so a chunk is owned by four
+// adjacent threads (one XXH lane each, 8 bytes of every 32-byte stripe); all
+// chunks run concurrently.  Not fused into the pack kernel: XXH64 is not
+// linear, partial results of different threads cannot be combined.
+constexpr unsigned long long kX1 = 0x9E3779B185EBCA87ULL, kX2 = 0xC2B2AE3D27D4EB4FULL,
+                             kX3 = 0x165667B19E3779F9ULL, kX4 = 0x85EBCA77C2B2AE63ULL,
+                             kX5 = 0x27D4EB2F165667C5ULL;
+__device__ __forceinline__ unsigned long long xrotl(unsigned long long x, int r) {
+  return (x << r) | (x >> (64 - r));
+}
+__device__ __forceinline__ unsigned long long xround(unsigned long long acc,
+                                                     unsigned long long in) {
+  return xrotl(acc + in * kX2, 31) * kX1;
+}
+__device__ __forceinline__ unsigned long long xmerge(unsigned long long h,
+                                                     unsigned long long v) {
+  return (h ^ xround(0, v)) * kX1 + kX4;
+}
+
+__global__ void __launch_bounds__(128) fcp_xxh64_kernel(const uint8_t* __restrict__ packed,
+                                                       uint64_t total, uint32_t chunk_bytes,
+                                                       uint64_t chunk_begin, uint64_t chunk_end,
+                                                       unsigned long long* __restrict__ out) {
+  const uint64_t t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const uint64_t chunk = chunk_begin + (t >> 2);
+  const int xl = static_cast<int>(t & 3);
+  const bool live = chunk < chunk_end;
+  const uint64_t cs = live ? chunk * chunk_bytes : 0;
+  uint64_t len = 0;
+  if (live) len = (cs + chunk_bytes <= total) ? chunk_bytes : total - cs;
+  const uint64_t n_stripes = len / 32;
+  const uint8_t* p = packed + cs + xl * 8;
+  unsigned long long v = xl == 0 ? kX1 + kX2 : xl == 1 ? kX2 : xl == 2 ? 0ULL : 0ULL - kX1;
+  uint64_t s = 0;
+  for (; s + 8 <= n_stripes; s += 8) {
+    unsigned long long w[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      w[k] = __ldg(reinterpret_cast<const unsigned long long*>(p + (s + k) * 32));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v = xround(v, w[k]);
+  }
+  for (; s < n_stripes; ++s)
+    v = xround(v, __ldg(reinterpret_cast<const unsigned long long*>(p + s * 32)));
+  // the four lanes of a chunk sit in lanes 4g..4g+3 of one warp
+  const int base = (threadIdx.x & 31) & ~3;
+  const unsigned long long v1 = __shfl_sync(0xffffffffu, v, base);
+  const unsigned long long v2 = __shfl_sync(0xffffffffu, v, base + 1);
+  const unsigned long long v3 = __shfl_sync(0xffffffffu, v, base + 2);
+  const unsigned long long v4 = __shfl_sync(0xffffffffu, v, base + 3);
+  if (!live || xl != 0) return;
+  unsigned long long h;
+  if (len >= 32) {
+    h = xrotl(v1, 1) + xrotl(v2, 7) + xrotl(v3, 12) + xrotl(v4, 18);
+    h = xmerge(xmerge(xmerge(xmerge(h, v1), v2), v3), v4);
+  } else {
+    h = kX5;
+  }
+  h += len;
+  const uint8_t* q = packed + cs + n_stripes * 32;
+  const uint8_t* end = packed + cs + len;
+  for (; q + 8 <= end; q += 8)
+    h = xrotl(h ^ xround(0, *reinterpret_cast<const unsigned long long*>(q)), 27) * kX1 + kX4;
+  if (q + 4 <= end) {
+    h = xrotl(h ^ (static_cast<unsigned long long>(*reinterpret_cast<const uint32_t*>(q)) * kX1),
+              23) * kX2 + kX3;
+    q += 4;
+  }
+  for (; q < end; ++q) h = xrotl(h ^ (static_cast<unsigned long long>(*q) * kX5), 11) * kX1;
+  h ^= h >> 33;
+  h *= kX2;
+  h ^= h >> 29;
+  h *= kX3;
+  h ^= h >> 32;
+  out[chunk] = h;
+}
+
 // One thread per chunk: Horner over the chunk's region values.  The value
 // written is the raw CRC of the chunk zero-padded to a whole number of
 // regions; the host strips the padding and applies init/xorout

@@ -91,6 +91,9 @@ class DeviceShardEngine(object):
         self.chunk_bytes = chunk_bytes
         self.checksum = _native.SUM_CRC32C if checksum else _native.SUM_NONE
         self.mode = _mode_from_env()
+        # optional second algorithm: standard XXH64 per chunk, computed on the
+        # staged image after the save is durable and re-checked after a restore
+        self.xxh64 = os.getenv("FCP_XXH64", "0") == "1" and self.mode != _native.MODE_DIRECT
         self._plan = None
         self._layout_key = None
         self._staging = None
@@ -241,10 +244,23 @@ class DeviceShardEngine(object):
         sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
         self._keepalive = []
         self.stats.update(self._plan.timings())
+        self.stats["xxh64"] = self._staged_xxh64() if self.xxh64 else None
         return sums
 
+    def _staged_xxh64(self):
+        """XXH64 (seed 0) of every chunk of the image now in HBM staging."""
+        plan = self._plan
+        if plan is None or self._staging is None or plan.total_bytes == 0:
+            return []
+        with torch.cuda.device(self.device):
+            out = torch.empty(plan.num_chunks, dtype=torch.int64, device=self.device)
+            stream = torch.cuda.current_stream(self.device)
+            _native.chunk_xxh64(self._staging.data_ptr(), plan.total_bytes, out.data_ptr(),
+                                self.chunk_bytes, stream.cuda_stream)
+            return [int(x) & 0xFFFFFFFFFFFFFFFF for x in out.cpu().tolist()]
+
     # -- restore ----------------------------------------------------------
-    def restore(self, leaves, total, buf, expected=None):
+    def restore(self, leaves, total, buf, expected=None, expected_xxh64=None):
         """Fill the tensors of `leaves` from the packed image in `buf`."""
         with torch.cuda.device(self.device):
             for lf in leaves:
@@ -286,6 +302,13 @@ class DeviceShardEngine(object):
             self.stats["restore_prepare_s"] = t_ready - t_begin
             self.stats["restore_move_s"] = t_moved - t_ready
             self.stats["restore_host_leaves_s"] = time.perf_counter() - t_moved
+            if expected_xxh64 is not None and self.xxh64:
+                got = self._staged_xxh64()
+                if got != list(expected_xxh64):
+                    bad = next(i for i, (a, b) in enumerate(zip(got, expected_xxh64)) if a != b)
+                    raise _native.ChecksumMismatch(
+                        -74, "XXH64 mismatch in chunk %d: expected %016x, got %016x"
+                        % (bad, expected_xxh64[bad], got[bad]))
 
     def restore_from_device(self, leaves, total, packed, expected=None):
         """Same, but the packed image is a device uint8 tensor (peer recovery)."""
@@ -325,9 +348,12 @@ class DeviceShardEngine(object):
         self._arena_pin = None
 
 
-def checksums_to_meta(sums, chunk_bytes):
-    return {"algo": "crc32c", "chunk_bytes": int(chunk_bytes),
-            "sums": np.asarray(sums, dtype=np.uint32).tolist()}
+def checksums_to_meta(sums, chunk_bytes, xxh64=None):
+    entry = {"algo": "crc32c", "chunk_bytes": int(chunk_bytes),
+             "sums": np.asarray(sums, dtype=np.uint32).tolist()}
+    if xxh64 is not None:
+        entry["xxh64"] = list(xxh64)
+    return entry
 
 
 def checksums_from_meta(entry, total, chunk_bytes):

@@ -143,6 +143,15 @@ int fcp_finish_checksums(const uint32_t* raw, uint64_t n_chunks,
                          uint64_t total_bytes, uint32_t chunk_bytes,
                          uint32_t* out);
 
+/* Second checksum algorithm (the reference has none): standard
+ * XXH64, seed 0, of every chunk of a DEVICE-resident packed image (the HBM
+ * staging after fcp_pack, or after the host->device copy of a restore);
+ * out[i] (device memory) receives the hash of chunk i.  XXH64 is not linear,
+ * so unlike CRC-32C it cannot be fused into the pack kernel: it is a second
+ * pass over the image, four threads per chunk, all chunks in flight.        */
+int fcp_chunk_xxh64(const void* packed, uint64_t total_bytes, uint32_t chunk_bytes,
+                    uint64_t* out, void* stream);
+
 /* Same work as fcp_launch over the WHOLE image, for callers that must not
  * allocate device memory.  No counterpart in the reference.
  *

@@ -194,3 +194,35 @@ def test_cold_restore_of_unpinned_segment_uses_bounce_ring():
     finally:
         writer.unlink()
         writer.close()
+
+
+def test_optional_xxh64_is_recorded_and_verified(monkeypatch):
+    monkeypatch.setenv("FCP_XXH64", "1")
+    torch.manual_seed(31)
+    tensors = {"w%d" % i: torch.randn(700001 + i, device="cuda") for i in range(6)}
+    sd = dict(tensors)
+    sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=2, paths={})
+    h = SharedMemoryHandler(44, host=True)
+    try:
+        h.save_state_dict(sd)
+        entry = h.metadata.get()[FCP_CHECKSUM_KEY]
+        total = h.shared_memory.size
+        image = np.frombuffer(h.shared_memory.buf, dtype=np.uint8)[:total]
+        chunk = entry["chunk_bytes"]
+        want = [oracle.xxh64(image[i * chunk:(i + 1) * chunk])
+                for i in range((total + chunk - 1) // chunk)]
+        assert entry["xxh64"] == want
+        del image
+        into = {k: torch.zeros_like(v) for k, v in tensors.items()}
+        h.load_state_dict(into=into)
+        for k, v in tensors.items():
+            assert torch.equal(into[k], v)
+        # a wrong recorded hash is noticed even though the CRCs agree
+        meta = h.metadata.get()
+        meta[FCP_CHECKSUM_KEY]["xxh64"][0] ^= 1
+        h.metadata.set(meta)
+        with pytest.raises(_native.ChecksumMismatch):
+            h.load_state_dict(into=into)
+    finally:
+        h.unlink()
+        h.close()

@@ -218,3 +218,19 @@ def test_empty_plan_and_bad_descriptors():
     bad = _native.make_descs([1, 2], [10, 5], [10, 10])  # overlapping / unordered
     with pytest.raises(_native.FcpError):
         _native.Plan(bad, 100, 0)
+
+
+@pytest.mark.parametrize("total,chunk", [(1, 64), (31, 64), (32, 64), (33, 64), (64, 64),
+                                         (1000, 256), (65536 * 3 + 77, 65536),
+                                         (5 * CHUNK + 123457, CHUNK)])
+def test_chunk_xxh64_matches_oracle(total, chunk):
+    rng = np.random.default_rng(total)
+    host = rng.integers(0, 256, total, dtype=np.uint8)
+    dev = torch.from_numpy(host).to(_dev())
+    n = (total + chunk - 1) // chunk
+    out = torch.zeros(n, dtype=torch.int64, device=_dev())
+    _native.chunk_xxh64(dev.data_ptr(), total, out.data_ptr(), chunk, _stream())
+    torch.cuda.synchronize()
+    got = [int(x) & 0xFFFFFFFFFFFFFFFF for x in out.cpu().tolist()]
+    want = [oracle.xxh64(host[i * chunk:(i + 1) * chunk]) for i in range(n)]
+    assert got == want

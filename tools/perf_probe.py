@@ -62,6 +62,11 @@ def main():
             best, med = timed(lambda: plan.scatter(staging.data_ptr(), cs, s()))
             out["scatter_%s_shift%d" % (name, shift)] = {
                 "ms": best, "ms_med": med, "GBps_2B": 2 * total / best / 1e6}
+        if shift == 0:
+            xo = torch.empty(plan.num_chunks, dtype=torch.int64, device="cuda")
+            best, med = timed(lambda: _native.chunk_xxh64(staging.data_ptr(), total,
+                                                          xo.data_ptr(), stream=s()))
+            out["xxh64_pass"] = {"ms": best, "ms_med": med, "GBps_1B": total / best / 1e6}
         if shift == 4 and not os.environ.get('PROBE_QUICK'):
             # host link
             mm = mmap.mmap(-1, total, flags=mmap.MAP_SHARED | mmap.MAP_POPULATE)
