@@ -161,8 +161,15 @@ class LocalSocketComm(metaclass=ABCMeta):
         return os.path.join(root, fname)
 
     def _init_socket(self):
+        # the socket listens from here on (clients queue in its backlog), but
+        # requests are served only after the subclass constructor has set the
+        # state they touch: see _serve()
         if self._create:
             self._server = _create_socket_server(self._socket_file)
+
+    def _serve(self):
+        """Last statement of every subclass constructor."""
+        if self._server is not None:
             threading.Thread(target=self._sync, daemon=True,
                              name="ipc-" + os.path.basename(self._socket_file)).start()
 
@@ -212,6 +219,7 @@ class SharedLock(LocalSocketComm):
     def __init__(self, name="", create=False):
         super().__init__(name, create)
         self._lock = threading.Lock() if self._create else None
+        self._serve()
 
     def _handle(self, request):
         if request.method == "acquire":
@@ -251,6 +259,7 @@ class SharedQueue(LocalSocketComm):
     def __init__(self, name="", create=False, maxsize=1):
         super().__init__(name, create)
         self._queue = queue.Queue(maxsize) if self._create else None
+        self._serve()
 
     def _handle(self, request):
         if request.method == "put":
@@ -302,6 +311,7 @@ class SharedDict(LocalSocketComm):
         super().__init__(name, create)
         self._dict = {}
         self._shared_queue = SharedQueue(name="shard_dict_" + name, create=self._create)
+        self._serve()
 
     def _handle(self, request):
         if request.method == "set":

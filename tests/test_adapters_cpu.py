@@ -258,3 +258,36 @@ def test_megatron_engines_and_dist_optimizer_state(saver_env):
                                              views[CheckpointConstant.OPTIM_STATES_NAME])
         assert torch.equal(p0.detach(), want[0])
         d.close()
+
+
+def test_hf_ddp_checkpointer_persists_every_captured_file(saver_env):
+    """The HF adapter's capture + persist step (the Trainer subclass itself
+    needs `accelerate`, which this image lacks): what the Trainer would
+    torch.save — weights, optimizer.pt, scheduler.pt, rng_state.pth — ends up
+    at exactly those paths, asynchronously."""
+    from dlrover_wuqiong_b200.flash_checkpoint._hijack import redirected
+    from dlrover_wuqiong_b200.flash_checkpoint.hf_trainer import HfDdpCheckpointer
+    model = SimpleNet()
+    optimizer = optim.AdamW(model.parameters(), lr=0.01)
+    model.fc2(model.fc1(torch.randn(2, 64))).sum().backward()
+    optimizer.step()
+    with tempfile.TemporaryDirectory() as tmpdir:
+        flash = HfDdpCheckpointer(tmpdir)
+        out = os.path.join(tmpdir, "checkpoint-8")
+        with redirected(save=flash.ckpt_agent.save):
+            torch.save(model.state_dict(), os.path.join(out, "pytorch_model.bin"))
+            torch.save(optimizer.state_dict(), os.path.join(out, "optimizer.pt"))
+            torch.save({"last_epoch": 8}, os.path.join(out, "scheduler.pt"))
+            torch.save({"cpu": torch.get_rng_state()}, os.path.join(out, "rng_state.pth"))
+        assert sorted(flash.ckpt_agent.paths) == ["optimizer.pt", "pytorch_model.bin",
+                                                  "rng_state.pth", "scheduler.pt"]
+        assert flash.save_checkpoint_to_storage(8)
+        tracker = os.path.join(tmpdir, CheckpointConstant.TRACER_FILE_NAME)
+        assert _wait_for(lambda: os.path.exists(tracker) and open(tracker).read() == "8")
+        assert sorted(os.listdir(out)) == ["optimizer.pt", "pytorch_model.bin", "rng_state.pth",
+                                          "scheduler.pt"]
+        back = torch.load(os.path.join(out, "pytorch_model.bin"), weights_only=False)
+        assert torch.equal(back["fc1.weight"], model.fc1.weight)
+        opt_back = torch.load(os.path.join(out, "optimizer.pt"), weights_only=False)
+        assert torch.equal(opt_back["state"][0]["exp_avg"], optimizer.state_dict()["state"][0]["exp_avg"])
+        flash.async_save_engine.close()
