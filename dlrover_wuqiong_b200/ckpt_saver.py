@@ -34,6 +34,7 @@ from typing import Dict, List, Optional
 import torch
 
 from . import plan as _plan
+from . import raw_ckpt
 from .common import env_utils
 from .common.constants import CheckpointConstant, NodeEnv
 from .common.log import default_logger as logger
@@ -349,6 +350,21 @@ class SharedMemoryHandler(object):
             return _read_state_dict_from_shm(_strip_private(meta_dict), self.shared_memory)
         return self._load_into(meta_dict, into, device)
 
+    def load_raw_images(self):
+        """{state name: RawImage} over the shm, for the saver's raw persist
+        format (raw_ckpt.py); {} when the shm holds no complete checkpoint."""
+        meta_dict = self.metadata.get()
+        config = meta_dict.get(DLROVER_CKPT_CONFIG_KEY, CheckpointConfig())
+        if not meta_dict or config.writing_shm:
+            return {}
+        if self.shared_memory is None or self._need_creation or self._segment_replaced():
+            self.init_shared_memory(create=False)
+        sums = meta_dict.get(FCP_CHECKSUM_KEY)
+        buf = self.shared_memory.buf if self.shared_memory else b""
+        return {name: raw_ckpt.RawImage(sub, buf, config.step, sums)
+                for name, sub in _strip_private(meta_dict).items()
+                if name != DLROVER_CKPT_CONFIG_KEY}
+
     def _load_into(self, meta_dict, into, device):
         total = self.shared_memory.size
         public = _strip_private(meta_dict)
@@ -411,6 +427,42 @@ class SharedMemoryHandler(object):
                         lf.tensor.copy_(src.view(lf.meta.dtype).reshape(lf.meta.shape)
                                         if lf.meta.offset % lf.meta.element_size == 0
                                         else src.clone().view(lf.meta.dtype).reshape(lf.meta.shape))
+
+    def restore_from_file(self, path, into):
+        """Fill the tensors of `into` (one state name's dict) from a raw image
+        file written by the saver (raw_ckpt.py).  CUDA tensors: file mapping ->
+        pinned ring -> HBM -> scatter kernel, CRC-verified when the file holds
+        the whole image; host tensors: copies.  Returns `into`'s structure
+        with the file's non-tensor leaves."""
+        header, data_off = raw_ckpt.read_header(path)
+        meta = raw_ckpt.decode_meta(header)
+        leaves = _plan.collect_leaves(into, meta, refresh=False)
+        if leaves is None or len(leaves) != _plan.count_tensor_metas(meta):
+            raise ValueError("`into` does not match the structure of the checkpoint in %s" % path)
+        total = header["nbytes"]
+        mm = raw_ckpt.map_payload(path, header, data_off)
+        engine = self._engine_for(leaves)
+        if engine is not None and mm is not None:
+            from .transfer import checksums_from_meta
+            image = header.get("image") or {}
+            expected = None
+            if image.get("offset") == 0:  # windows line up with the payload
+                expected = checksums_from_meta(image.get("checksums"), total, engine.chunk_bytes)
+            engine.restore(leaves, total, mm, expected, transient=True)
+            self.last_stats = dict(engine.stats)
+        elif mm is not None:
+            for lf in leaves:
+                if lf.nbytes:
+                    src = torch.frombuffer(mm, dtype=lf.meta.dtype, count=lf.meta.numel,
+                                           offset=lf.meta.offset).reshape(lf.meta.shape)
+                    with torch.no_grad():
+                        lf.tensor.copy_(src)
+        it = iter(leaves)
+
+        def fill(m):
+            return next(it).tensor if isinstance(m, TensorMeta) else m
+
+        return _traverse_state_dict(meta, fill)
 
     def _segment_replaced(self):
         """The writer re-creates the segment when the layout changes; a reader
@@ -704,6 +756,19 @@ class AsyncCheckpointSaver(metaclass=ABCMeta):
                 logger.info("timeout syncing the checkpoint step; some nodes may have failed")
                 return False
 
+    def _persist_states(self, local_shard_id, ckpt_config):
+        """Write every state name that has a path: ``torch.save`` of views
+        over the shm (SAVER:914-921), or with DLROVER_FCP_PERSIST_FORMAT=raw
+        the image bytes themselves (raw_ckpt.py)."""
+        handler = self._shm_handlers[local_shard_id]
+        if raw_ckpt.persist_format() == "raw":
+            states, write_func = handler.load_raw_images(), raw_ckpt.write_raw
+        else:
+            states, write_func = handler.load_state_dict(), torch.save
+        for state_name, sd in states.items():
+            if sd and state_name in ckpt_config.paths:
+                self.storage.write_state_dict(sd, ckpt_config.paths[state_name], write_func)
+
     @abstractmethod
     def save_step_checkpoint(self, step: int):
         """Persist the checkpoint of `step` from shm to storage."""
@@ -773,10 +838,7 @@ class CommonDirCheckpointSaver(AsyncCheckpointSaver):
         self.storage.commit(step, success)
 
     def persist_to_storage(self, local_shard_id, ckpt_config):
-        state_dict = self._shm_handlers[local_shard_id].load_state_dict()
-        for state_name, sd in state_dict.items():
-            if sd and state_name in ckpt_config.paths:
-                self.storage.write_state_dict(sd, ckpt_config.paths[state_name], torch.save)
+        self._persist_states(local_shard_id, ckpt_config)
 
 
 class TempDirCheckpointSaver(AsyncCheckpointSaver):
@@ -865,10 +927,7 @@ class TempDirCheckpointSaver(AsyncCheckpointSaver):
         self.storage.commit(step, success)
 
     def persist_to_storage(self, local_shard_id, ckpt_config):
-        state_dict = self._shm_handlers[local_shard_id].load_state_dict()
-        for state_name, sd in state_dict.items():
-            if sd and state_name in ckpt_config.paths:
-                self.storage.write_state_dict(sd, ckpt_config.paths[state_name], torch.save)
+        self._persist_states(local_shard_id, ckpt_config)
 
 
 class DdpCheckpointSaver(CommonDirCheckpointSaver):

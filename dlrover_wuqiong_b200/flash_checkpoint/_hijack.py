@@ -7,8 +7,18 @@ import contextlib
 
 import torch
 
+from .. import raw_ckpt
+
 torch_native_save = torch.save
 torch_native_load = torch.load
+
+
+def _read_file(path, map_location=None):
+    """Read a persisted state: raw image (raw_ckpt.py) or torch.save file,
+    with the un-intercepted torch.load."""
+    if isinstance(path, str) and raw_ckpt.is_raw(path):
+        return raw_ckpt.read_raw(path)
+    return torch_native_load(path, map_location=map_location, weights_only=False)
 
 
 @contextlib.contextmanager

@@ -16,7 +16,7 @@ from ..ckpt_saver import DeepSpeedCheckpointSaver
 from ..common import env_utils
 from ..common.constants import CheckpointConstant
 from ..common.storage import CheckpointStorage, get_checkpoint_storage
-from ._hijack import redirected, torch_native_load, torch_native_save
+from ._hijack import _read_file, redirected, torch_native_save
 from .checkpointer import Checkpointer, StorageType
 from .deepspeed_engine import DeepSpeedCheckpointEngine
 
@@ -64,7 +64,7 @@ class AsyncCheckpointAgent(object):
         if name in self.state_dict:
             return self.state_dict[name]
         return self.storage.read_state_dict(
-            path, lambda p: torch_native_load(p, map_location=map_location, weights_only=False))
+            path, lambda p: _read_file(p, map_location))
 
     def commit(self, tag):
         pass

@@ -13,6 +13,7 @@ from ..ckpt_saver import (
     CheckpointEventType,
     DdpCheckpointSaver,
 )
+from .. import raw_ckpt
 from ..common import env_utils
 from ..common.constants import CheckpointConstant
 from ..common.log import default_logger as logger
@@ -91,11 +92,21 @@ class FullCheckpointEngine(CheckpointEngine):
                 raise ValueError("The checkpoint shared memory must hold the state dict "
                                  "of one path only. Now, paths are %s" % names)
             return state_dict[names[0]]
-        return self._load_from_storage(resume_path)
+        if into is not None:
+            names = list(into.keys())
+            into = into[names[0]] if len(names) == 1 else None
+        return self._load_from_storage(resume_path, into=into)
 
-    def _load_from_storage(self, resume_path=""):
+    def _load_from_storage(self, resume_path="", into=None):
+        """`into`: the live state dict to fill in place (raw image files go
+        file -> pinned ring -> scatter kernel; torch.save files are loaded on
+        the host and copied leaf by leaf)."""
         def read(path):
-            return torch.load(path, map_location="cpu", weights_only=False)
+            if into is None:
+                return raw_ckpt.load_any(path, map_location="cpu")
+            if raw_ckpt.is_raw(path):
+                return self._shm_handler.restore_from_file(path, into)
+            return _copy_into(into, raw_ckpt.load_any(path, map_location="cpu"))
 
         if resume_path:
             return self.storage.read_state_dict(resume_path, read_func=read)
@@ -111,3 +122,18 @@ class FullCheckpointEngine(CheckpointEngine):
         # unsharded: every rank reads what rank 0 wrote
         who = 0 if self._global_shard_num == 1 else self._rank
         return os.path.join(self.checkpoint_dir, "%s/rank_%s.pt" % (iteration, who))
+
+
+def _copy_into(into, loaded):
+    """Copy every tensor of `loaded` into the tensor at the same place of
+    `into`; returns `loaded`'s structure holding `into`'s tensors."""
+    if isinstance(loaded, dict):
+        return {k: _copy_into(into[k], v) if isinstance(v, (dict, list)) or torch.is_tensor(v)
+                else v for k, v in loaded.items()}
+    if isinstance(loaded, list):
+        return [_copy_into(into[i], v) if isinstance(v, (dict, list)) or torch.is_tensor(v)
+                else v for i, v in enumerate(loaded)]
+    if loaded.numel():
+        with torch.no_grad():
+            into.copy_(loaded)
+    return into

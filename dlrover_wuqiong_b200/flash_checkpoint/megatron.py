@@ -18,7 +18,7 @@ from ..common.constants import CheckpointConstant
 from ..common.log import default_logger as logger
 from ..common.singleton import Singleton
 from ..common.storage import PosixDiskStorage
-from ._hijack import redirected, torch_native_load, torch_native_save
+from ._hijack import _read_file, redirected, torch_native_load, torch_native_save
 from .checkpointer import StorageType
 from .megatron_engine import MegatronCheckpointEngine
 
@@ -80,8 +80,7 @@ class MegatronCheckpointer(Singleton):
         name = _state_name(path)
         if name and name in state_dict:
             return state_dict[name]
-        return self.storage.read_state_dict(
-            path, lambda p: torch_native_load(p, map_location="cpu", weights_only=False))
+        return self.storage.read_state_dict(path, lambda p: _read_file(p, "cpu"))
 
     def update_tracer_file(self, iteration: int):
         """Megatron's save created ``iter_XXXXXXX/`` and advanced its tracker

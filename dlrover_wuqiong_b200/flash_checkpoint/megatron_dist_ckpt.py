@@ -27,6 +27,7 @@ from ..common.storage import (  # noqa: F401  (re-exported, as the reference doe
     PosixDiskStorage,
     get_checkpoint_storage,
 )
+from ._hijack import _read_file
 from .checkpointer import StorageType
 from .megatron_engine import MegatronCheckpointEngine, MegatronDistCheckpointEngine
 
@@ -217,8 +218,8 @@ def _load_base_checkpoint(load_dir, rank0=False):
         checkpoint_name = mg["get_checkpoint_name"](load_dir, iteration, release)
     opt_name = get_dist_optimizer_checkpoint_name(load_dir, iteration, release)
     try:
-        model_sd = torch.load(checkpoint_name, map_location="cpu", weights_only=False)
-        opt_sd = torch.load(opt_name, map_location="cpu", weights_only=False) \
+        model_sd = _read_file(checkpoint_name, "cpu")
+        opt_sd = _read_file(opt_name, "cpu") \
             if os.path.exists(opt_name) else {}
     except BaseException as e:  # noqa: BLE001 - Megatron exits here too
         mg["print_rank_0"]("could not load the checkpoint: %s" % e)

@@ -260,8 +260,10 @@ class DeviceShardEngine(object):
             return [int(x) & 0xFFFFFFFFFFFFFFFF for x in out.cpu().tolist()]
 
     # -- restore ----------------------------------------------------------
-    def restore(self, leaves, total, buf, expected=None, expected_xxh64=None):
-        """Fill the tensors of `leaves` from the packed image in `buf`."""
+    def restore(self, leaves, total, buf, expected=None, expected_xxh64=None, transient=False):
+        """Fill the tensors of `leaves` from the packed image in `buf`.
+        `transient`: `buf` is not the shm segment (e.g. a mapped checkpoint
+        file): stream it through the pinned ring, pin nothing."""
         with torch.cuda.device(self.device):
             for lf in leaves:
                 if lf.is_cuda and lf.nbytes and not lf.tensor.is_contiguous():
@@ -270,6 +272,9 @@ class DeviceShardEngine(object):
             ptrs, offs, sizes, host = self._sources(leaves)
             plan = self._ensure_plan(ptrs, offs, sizes, total)
             stream = torch.cuda.current_stream(self.device)
+            if transient and total and self._staging is None:  # direct mode keeps none
+                self._staging = torch.empty(plan.staging_bytes, dtype=torch.uint8,
+                                            device=self.device)
             staging_ptr = self._staging.data_ptr() if self._staging is not None else None
             checksum = self.checksum if expected is not None else _native.SUM_NONE
             self._join_mapping_job()
@@ -277,7 +282,13 @@ class DeviceShardEngine(object):
             t_ready = time.perf_counter()
             cold = (self._mapping is None or self._mapping.addr != buffer_address(buf)
                     or self._mapping.nbytes < total)
-            if (cold and total and self.mode != _native.MODE_DIRECT
+            if transient:
+                if total:
+                    plan.restore_bounced(buffer_address(buf), staging_ptr, checksum, expected,
+                                         int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
+                                         stream.cuda_stream)
+                self.stats["restore_path"] = "bounced_file"
+            elif (cold and total and self.mode != _native.MODE_DIRECT
                     and os.getenv("FCP_COLD_RESTORE", "bounce") == "bounce"):
                 # fresh process, segment not pinned yet: stream it through the
                 # pinned ring now, pin it in the background for later saves

@@ -226,3 +226,72 @@ def test_optional_xxh64_is_recorded_and_verified(monkeypatch):
     finally:
         h.unlink()
         h.close()
+
+
+def test_raw_persisted_file_restores_in_place_through_the_scatter_kernel(monkeypatch):
+    """DLROVER_FCP_PERSIST_FORMAT=raw: the agent writes the shm image itself;
+    a trainer whose memory checkpoint is gone restores that file straight into
+    its CUDA tensors (file mapping -> pinned ring -> scatter kernel, CRC
+    verified), and the same file still reads as the reference's state dict."""
+    import time
+
+    from dlrover_wuqiong_b200 import raw_ckpt
+    from dlrover_wuqiong_b200.common.constants import CheckpointConstant
+
+    monkeypatch.setenv(NodeEnv.NODE_NUM, "1")
+    monkeypatch.setenv(NodeEnv.NODE_RANK, "0")
+    monkeypatch.setenv(raw_ckpt.PERSIST_FORMAT_ENV, "raw")
+    AsyncCheckpointSaver._saver_instance = None
+    AsyncCheckpointSaver.start_async_saving_ckpt()
+    try:
+        torch.manual_seed(17)
+        model = nn.Sequential(nn.Linear(1024, 2048), nn.Linear(2048, 1031)).cuda()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-3, fused=True)
+        model(torch.randn(4, 1024, device="cuda")).sum().backward()
+        opt.step()
+        with tempfile.TemporaryDirectory() as tmpdir:
+            ckpt = DdpCheckpointer(tmpdir)
+            sd = {"model": model.state_dict(), "optimizer": opt.state_dict(), "step": 30}
+            meta, total, expect = oracle.pack(sd)
+            ref = oracle.unpack(meta, expect)
+            assert ckpt.save_checkpoint(30, sd, storage_type=StorageType.DISK)
+            tracker = os.path.join(tmpdir, CheckpointConstant.TRACER_FILE_NAME)
+            t0 = time.time()
+            while not (os.path.exists(tracker) and open(tracker).read() == "30"):
+                assert time.time() - t0 < 30, "the agent did not persist step 30"
+                time.sleep(0.1)
+            path = os.path.join(tmpdir, "30", "rank_0.pt")
+            header, data_off = raw_ckpt.read_header(path)
+            with open(path, "rb") as f:
+                f.seek(data_off)
+                assert f.read() == expect.tobytes()  # the reference's bytes
+            # memory checkpoint gone -> storage, in place
+            ckpt._engine._shm_handler.metadata.set({})
+            into = {"model": {k: torch.zeros_like(v) for k, v in sd["model"].items()},
+                    "optimizer": {"state": {i: {k: torch.zeros_like(v) for k, v in st.items()}
+                                            for i, st in sd["optimizer"]["state"].items()},
+                                  "param_groups": sd["optimizer"]["param_groups"]},
+                    "step": 0}
+            back = ckpt.load_checkpoint(into=into)
+            assert ckpt._engine._shm_handler.last_stats["restore_path"] == "bounced_file"
+            assert back["step"] == 30
+            for k in sd["model"]:
+                assert into["model"][k].is_cuda
+                assert torch.equal(into["model"][k].cpu(), ref["model"][k]), k
+            for i, st in ref["optimizer"]["state"].items():
+                for k, v in st.items():
+                    assert torch.equal(into["optimizer"]["state"][i][k].cpu(), v), (i, k)
+            # one flipped payload bit on disk is caught by the kernel's CRC
+            with open(path, "r+b") as f:
+                f.seek(data_off + total // 2)
+                b = f.read(1)
+                f.seek(data_off + total // 2)
+                f.write(bytes([b[0] ^ 0x10]))
+            with pytest.raises(_native.ChecksumMismatch):
+                ckpt.load_checkpoint(path, into=into)
+            ckpt.close()
+    finally:
+        if AsyncCheckpointSaver._saver_instance:
+            AsyncCheckpointSaver._saver_instance.close()
+            AsyncCheckpointSaver._saver_instance = None
+        clear_sock_dir()

@@ -234,3 +234,70 @@ def test_chunk_xxh64_matches_oracle(total, chunk):
     got = [int(x) & 0xFFFFFFFFFFFFFFFF for x in out.cpu().tolist()]
     want = [oracle.xxh64(host[i * chunk:(i + 1) * chunk]) for i in range(n)]
     assert got == want
+
+
+def test_image_beyond_4gib_by_properties():
+    """Full-size behaviour without a CPU pass over every byte: an image that
+    crosses 2^32 (64-bit offsets in descriptors, regions and chunks), checked
+    by (1) device-side equality of every tensor's slot in the image, (2) the
+    oracle's CRC on sampled chunks (first, last, around 2^32, around tensor
+    boundaries), (3) scatter(pack(x)) == x with the same sums (idempotence),
+    (4) CRC linearity: crc(a^b) = crc(a)^crc(b)^crc(0) per chunk."""
+    torch.manual_seed(77)
+    dev = _dev()
+    sizes = [(1 << 32) // 4 - 3, 1, (300 << 20) // 4 + 5, 7, (1 << 30) // 4 + 1]  # fp32 elements
+    flat, off = [], 0
+    for i, n in enumerate(sizes):
+        t = torch.empty(n, dtype=torch.float32, device=dev)
+        t.view(torch.int32).random_(-2**31, 2**31 - 1)
+        flat.append((t, oracle.OMeta((n,), torch.float32, 4, n, off)))
+        off += 4 * n
+        if i == 1:  # a bf16 scalar: everything behind it sits at 2 mod 4
+            s = torch.randn((), device=dev).to(torch.bfloat16)
+            flat.append((s, oracle.OMeta((), torch.bfloat16, 2, 1, off)))
+            off += 2
+    total = off
+    assert total > (1 << 32) + (1 << 30)
+    plan, keep = _plan_for(flat, total)
+    staging = torch.zeros(plan.staging_bytes, dtype=torch.uint8, device=dev)
+    plan.pack(staging.data_ptr(), _native.SUM_CRC32C, _stream())
+    torch.cuda.synchronize()
+    sums = plan.read_checksums(_stream())
+    # (1) every tensor's bytes sit at its offset
+    for t, m in flat:
+        n = m.numel * m.element_size
+        assert torch.equal(staging[m.offset:m.offset + n], t.reshape(-1).view(torch.uint8)), m.offset
+    # (2) sampled chunks against the oracle
+    n_chunks = (total + CHUNK - 1) // CHUNK
+    assert len(sums) == n_chunks
+    picks = {0, 1, n_chunks - 2, n_chunks - 1, (1 << 32) // CHUNK - 1, (1 << 32) // CHUNK}
+    for t, m in flat:
+        picks.add(m.offset // CHUNK)
+    for c in sorted(picks):
+        lo, hi = c * CHUNK, min((c + 1) * CHUNK, total)
+        want = oracle.chunk_crc32c(staging[lo:hi].cpu().numpy(), CHUNK)
+        assert int(sums[c]) == int(want[0]), c
+    # (3) scatter into fresh tensors: same bytes, same sums
+    fresh = [torch.zeros_like(t) for t, m in flat]
+    plan.update_ptrs([t.data_ptr() for t in fresh])
+    plan.scatter(staging.data_ptr(), _native.SUM_CRC32C, _stream())
+    torch.cuda.synchronize()
+    for (a, _), b in zip(flat, fresh):
+        assert torch.equal(a.reshape(-1).view(torch.uint8), b.reshape(-1).view(torch.uint8))
+    assert plan.read_checksums(_stream()).tolist() == sums.tolist()
+    del fresh, staging
+    plan.close()
+
+    # (4) linearity on a 96 MiB image (three packs)
+    n = (96 << 20) // 4 + 3
+    a = torch.empty(n, dtype=torch.int32, device=dev).random_(-2**31, 2**31 - 1)
+    b = torch.empty(n, dtype=torch.int32, device=dev).random_(-2**31, 2**31 - 1)
+    crcs = []
+    for x in (a, b, a ^ b, torch.zeros_like(a)):
+        p, _ = _plan_for([(x, oracle.OMeta((n,), torch.int32, 4, n, 0))], 4 * n)
+        st = torch.empty(p.staging_bytes, dtype=torch.uint8, device=dev)
+        p.pack(st.data_ptr(), _native.SUM_CRC32C, _stream())
+        torch.cuda.synchronize()
+        crcs.append(np.asarray(p.read_checksums(_stream()), dtype=np.uint32))
+        p.close()
+    assert np.array_equal(crcs[2], crcs[0] ^ crcs[1] ^ crcs[3])
