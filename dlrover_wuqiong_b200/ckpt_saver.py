@@ -313,7 +313,8 @@ class SharedMemoryHandler(object):
             # lock for the whole save, so the agent cannot read in between;
             # a trainer that dies in the ~2 ms window leaves the lock held
             # (agent skips the shard) and a torn image fails its CRC.
-            engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf)
+            engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf,
+                              ready=getattr(self.shared_memory, "wait_populated", None))
             self._announce(meta_dict, conf)
             return PendingSave(self, meta_dict, conf, engine)
         self._announce(meta_dict, conf)

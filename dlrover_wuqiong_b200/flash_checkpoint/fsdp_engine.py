@@ -169,7 +169,8 @@ class SharedMemoryWriter(StorageWriter):
         if offset:
             engine = h._engine_for(leaves)
             if engine is not None:
-                engine.save_begin(leaves, offset, h.shared_memory.buf)
+                engine.save_begin(leaves, offset, h.shared_memory.buf,
+                                  ready=getattr(h.shared_memory, "wait_populated", None))
                 sums = engine.save_finish()
                 h.last_stats = dict(engine.stats)
                 if sums is not None:

@@ -56,10 +56,15 @@ class HostMapping(object):
         self.register_s = 0.0
         self.complete = False
 
-    def register_all(self, pause=0.0):
+    def register_all(self, pause=0.0, ready=None):
+        """`ready(upto)`: called before a piece is pinned; returns once the
+        first `upto` bytes of the segment are resident (a segment that is still
+        being populated in the background, SharedMemory.wait_populated)."""
         t0 = time.time()
         step = self.piece if self.piece else max(self.nbytes, 1)
         for off in range(0, self.nbytes, step):
+            if ready is not None:
+                ready(min(off + step, self.nbytes))
             _native.host_register(self.addr + off, min(step, self.nbytes - off))
             self._done.append(off)
             if pause:
@@ -205,7 +210,7 @@ class DeviceShardEngine(object):
     def _piece_bytes(self):
         return 0 if self.mode == _native.MODE_DIRECT else REGISTER_PIECE_BYTES
 
-    def _ensure_mapping(self, buf, total):
+    def _ensure_mapping(self, buf, total, ready=None):
         self._join_mapping_job()
         addr = buffer_address(buf)
         if self._mapping is not None and (self._mapping.addr != addr
@@ -214,22 +219,23 @@ class DeviceShardEngine(object):
             self._mapping.close()
             self._mapping = None
         if self._mapping is None and total:
-            self._mapping = HostMapping(buf, total, self._piece_bytes()).register_all()
+            self._mapping = HostMapping(buf, total, self._piece_bytes()).register_all(ready=ready)
             self.stats["register_s"] = self._mapping.register_s
         if self._plan is not None:
             self._plan.set_copy_piece_bytes(self._piece_bytes())
         return addr
 
     # -- save -------------------------------------------------------------
-    def save_begin(self, leaves, total, buf):
+    def save_begin(self, leaves, total, buf, ready=None):
         """Enqueue pack + transfer of the shard into `buf`; returns once the
         work is enqueued.  Call save_packed_wait() before mutating the tensors
-        and save_finish() for durability + checksums."""
+        and save_finish() for durability + checksums.  `ready`: see
+        HostMapping.register_all."""
         with torch.cuda.device(self.device):
             t0 = time.perf_counter()
             ptrs, offs, sizes, host = self._sources(leaves)
             plan = self._ensure_plan(ptrs, offs, sizes, total)
-            addr = self._ensure_mapping(buf, total)
+            addr = self._ensure_mapping(buf, total, ready)
             stream = torch.cuda.current_stream(self.device)
             self._stage_host_leaves(host, to_device=True)
             t1 = time.perf_counter()

@@ -420,3 +420,36 @@ def test_meta_delta_updates_between_trainer_and_agent():
         trainer.close()
         agent.unlink()
         agent.close()
+
+
+def test_shared_memory_is_populated_in_the_background(monkeypatch):
+    """A created segment becomes resident from worker threads; wait_populated
+    follows the front in address order and close() joins the workers."""
+    import dlrover_wuqiong_b200.common.multi_process as mp
+    monkeypatch.setattr(mp, "_POPULATE_BLOCK", 1 << 20)
+    name = "fcp_test_populate_%d" % os.getpid()
+    size = (7 << 20) + 12345
+    shm = SharedMemory(name=name, create=True, size=size)
+    try:
+        shm.wait_populated(3 << 20)
+        shm.wait_populated()
+        assert shm._populator is None
+        assert bytes(shm.buf[:64]) == b"\0" * 64 and shm.buf[size - 1] == 0
+        shm.buf[size - 1] = 7
+        other = SharedMemory(name=name)  # attaching does not populate
+        assert other._populator is None and other.buf[size - 1] == 7
+        other.close()
+    finally:
+        shm.close()
+        shm.unlink()
+    # closing right after creation must not leave workers touching unmapped memory
+    shm = SharedMemory(name=name, create=True, size=size)
+    shm.close()
+    shm.unlink()
+    # FCP_POPULATE_THREADS=0: no background work at all
+    monkeypatch.setenv("FCP_POPULATE_THREADS", "0")
+    shm = SharedMemory(name=name, create=True, size=4096)
+    assert shm._populator is None
+    shm.wait_populated()
+    shm.close()
+    shm.unlink()
