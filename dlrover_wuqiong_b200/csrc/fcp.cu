@@ -190,6 +190,7 @@ struct fcp_plan {
   std::vector<fcp_desc> h_descs;
   fcp_desc* d_descs = nullptr;
   uint32_t* d_region_sums = nullptr;
+  uint32_t* d_work = nullptr;  // run-distribution counters of the kernels (Args.work)
   uint32_t* d_chunk_sums = nullptr;
   uint32_t* h_chunk_sums = nullptr;  // pinned
   cudaStream_t copy_stream = nullptr;
@@ -235,6 +236,7 @@ fcpk::Args plan_args(const fcp_plan* p, void* packed, uint64_t rb, uint64_t re) 
   a.region_sums = p->d_region_sums;
   a.run = 1;
   a.flags = p->kernel_flags;
+  a.work = std::getenv("FCP_DEBUG_STATIC_RUNS") ? nullptr : p->d_work;
   return a;
 }
 
@@ -378,6 +380,8 @@ int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
                      sizeof(uint32_t) * (p->n_regions ? p->n_regions : 1)));
   FCP_TRY(cudaMalloc(&p->d_chunk_sums,
                      sizeof(uint32_t) * (p->n_chunks ? p->n_chunks : 1)));
+  FCP_TRY(cudaMalloc(&p->d_work, 256));
+  FCP_TRY(cudaMemset(p->d_work, 0, 256));
   FCP_TRY(cudaMallocHost(&p->h_chunk_sums,
                          sizeof(uint32_t) * (p->n_chunks ? p->n_chunks : 1)));
   FCP_TRY(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
@@ -416,6 +420,7 @@ void fcp_plan_destroy(fcp_plan* p) {
   if (p->copy_stream) cudaStreamSynchronize(p->copy_stream);
   if (p->d_descs) cudaFree(p->d_descs);
   if (p->d_region_sums) cudaFree(p->d_region_sums);
+  if (p->d_work) cudaFree(p->d_work);
   if (p->d_chunk_sums) cudaFree(p->d_chunk_sums);
   if (p->h_chunk_sums) cudaFreeHost(p->h_chunk_sums);
   if (p->ring) cudaFreeHost(p->ring);
@@ -588,6 +593,7 @@ int fcp_launch(const fcp_desc* descs_dev, uint64_t n, uint64_t total_bytes,
   a.region_sums = region_sums;
   a.run = 1;
   a.flags = 0;
+  a.work = nullptr;  // static striding: no counters to own here
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   rc = launch_any(a, direction, checksum, dev, st);
   if (rc) return rc;
@@ -1042,6 +1048,7 @@ extern "C" int fcp_launch_noalloc(const fcp_desc* descs_dev, uint64_t n,
   a.region_sums = scratch;
   a.run = 1;
   a.flags = 0;
+  a.work = nullptr;  // static striding: no counters to own here
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   rc = launch_any(a, direction, checksum, dev, st);
   if (rc) return rc;

@@ -268,6 +268,7 @@ struct Args {
   uint32_t* region_sums;
   uint32_t run;    // regions per warp visit, set by the launcher
   uint32_t flags;  // kNoPrefetch: the read side is peer memory (never in local L2)
+  uint32_t* work;  // two zeroed counters for dynamic run distribution, or nullptr
 };
 constexpr uint32_t kNoPrefetch = 1u;
 
