@@ -268,7 +268,7 @@ int fcp_plan_set_read_prefetch(fcp_plan* plan, int enable);
 /* Number of kernels the last fcp_save_async / fcp_restore launched.          */
 uint64_t fcp_plan_last_launches(const fcp_plan* plan);
 /* Smallest slice of the staged pipelines (multiple of chunk_bytes; default
- * 1 GiB).  Slices double in size up to 4x this value; a save runs the
+ * 1 GiB).  Slices grow 4x per step up to 16x this value; a save runs the
  * schedule small-to-large, a restore large-to-small.                        */
 int fcp_plan_set_slice_bytes(fcp_plan* plan, uint64_t slice_bytes);
 
