@@ -29,6 +29,9 @@ import torch.distributed as dist  # noqa: E402
 
 GB = 1e9
 PCIE_GEN5_X16_GBS = 64.0
+# dram__bytes_read.sum + dram__bytes_write.sum over the pack launches of one save
+# (ncu --set full capture of this program, profiles/r01_ncu_pack_v3_summary.md)
+NCU_TRAFFIC_BYTES = {("gpt2-xl-1.5B-adamw-fp32", 0): 39.10e9}
 _REAL_STDOUT = sys.stdout
 
 WORKLOADS = {
@@ -600,7 +603,12 @@ def run_ours(args, rank, local_rank, world):
             "first_save_s": first_save_s, "host_register_s": register_s,
             "roofline": {"bound": "hbm", "kernel": "fcp_kernel<PACK,CRC,32,1024> (pack + fused CRC32C)",
                          "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / hbm_peak,
+                         "traffic": NCU_TRAFFIC_BYTES.get((workload, mode)),
+                         "traffic_unit": "bytes per launch set (dram read + write of one save's "
+                                         "pack launches, ncu --set full, "
+                                         "profiles/r01_ncu_pack_v3_summary.md)",
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch_set": 2 * B},
             "cpu_baseline": cpu_base,
             "reference_loop_gpu_source": ref_gpu,
