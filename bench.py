@@ -586,6 +586,8 @@ def run_ours(args, rank, local_rank, world):
                 "workload": workload, "shard_bytes_per_rank": B, "tensors_per_rank": n_tensors,
                 "step": "save HBM->shm (durable, CRC32C/2MiB) + restore shm->live tensors (verified)",
                 "transfer_mode": {0: "staged", 1: "direct", 2: "staged_kernel"}[mode],
+                "transfer_mode_chosen_at_run_time": (
+                    dict(eng.tuner.rates, state=eng.tuner.state) if eng.tuner is not None else None),
                 "l2": "inputs (%.1f GB) larger than L2" % (B / GB), "note": note,
                 "host_link_peak_GBps_per_dir": PCIE_GEN5_X16_GBS},
             "save_blocking_s": save_blocking_s,

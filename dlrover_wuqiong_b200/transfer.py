@@ -22,12 +22,63 @@ CHECKSUM_KEY = "_FCP_CHECKSUMS"  # extra top-level meta key (ignored by savers)
 
 
 def _mode_from_env():
-    """FCP_TRANSFER_MODE = staged (copy engine, default) | staged_kernel (copy
-    kernel for the device->host leg) | direct (pack kernel writes the host
-    segment itself)."""
+    """FCP_TRANSFER_MODE = auto (default: staged, with the device->host leg
+    chosen at run time, see SaveLegTuner) | staged (copy engine) |
+    staged_kernel (copy kernel for the device->host leg) | direct (pack kernel
+    writes the host segment itself)."""
     return {"direct": _native.MODE_DIRECT,
             "staged_kernel": _native.MODE_STAGED_KERNEL}.get(
-                os.getenv("FCP_TRANSFER_MODE", "staged"), _native.MODE_STAGED)
+                os.getenv("FCP_TRANSFER_MODE", "auto"), _native.MODE_STAGED)
+
+
+class SaveLegTuner(object):
+    """Chooses the device->host leg of staged saves from what this process
+    measures on this host.
+
+    The copy engine is free (no SMs) and sustains ~57 GB/s on a Gen5 x16 link,
+    so it is the default.  On some multi-GPU hosts concurrent copy-engine
+    *writes* into host memory stop scaling (measured: 33.5 GB/s/rank at 2
+    GPUs, 9.8 at 8) while SM stores into the mapped segment keep more of the
+    link (51 and 11.6 GB/s/rank).  So: if a copy-engine save of >= 1 GiB runs
+    below GOOD_GBPS, the next save tries the copy kernel and the faster of the
+    two (by > 10 %) is kept.  The very first save of a process is not used as
+    a sample."""
+
+    MIN_BYTES = 1 << 30
+    GOOD_GBPS = 45.0  # 0.8 x what the copy engine sustains on an idle link
+
+    def __init__(self):
+        self.state = "warmup"  # -> engine_probe -> [kernel_probe] -> settled
+        self.rates = {}
+        self.choice = _native.MODE_STAGED
+
+    @property
+    def settled(self):
+        return self.state == "settled"
+
+    def mode(self):
+        return _native.MODE_STAGED_KERNEL if self.state == "kernel_probe" else self.choice
+
+    def kernel_leg_failed(self):
+        self.state, self.choice = "settled", _native.MODE_STAGED
+
+    def report(self, mode, nbytes, seconds):
+        if self.settled or nbytes < self.MIN_BYTES or seconds <= 0:
+            return
+        rate = nbytes / seconds / 1e9
+        if self.state == "warmup":
+            self.state = "engine_probe"
+        elif self.state == "engine_probe":
+            self.rates["engine"] = rate
+            self.state = "settled" if rate >= self.GOOD_GBPS else "kernel_probe"
+        elif self.state == "kernel_probe" and mode == _native.MODE_STAGED_KERNEL:
+            self.rates["kernel"] = rate
+            if rate > 1.1 * self.rates["engine"]:
+                self.choice = _native.MODE_STAGED_KERNEL
+            self.state = "settled"
+            logger.info("device->host leg: copy engine %.1f GB/s, copy kernel %.1f GB/s -> %s",
+                        self.rates["engine"], rate,
+                        "copy kernel" if self.choice == _native.MODE_STAGED_KERNEL else "copy engine")
 
 
 def buffer_address(buf):
@@ -96,6 +147,7 @@ class DeviceShardEngine(object):
         self.chunk_bytes = chunk_bytes
         self.checksum = _native.SUM_CRC32C if checksum else _native.SUM_NONE
         self.mode = _mode_from_env()
+        self.tuner = SaveLegTuner() if os.getenv("FCP_TRANSFER_MODE", "auto") == "auto" else None
         # optional second algorithm: standard XXH64 per chunk, computed on the
         # staged image after the save is durable and re-checked after a restore
         self.xxh64 = os.getenv("FCP_XXH64", "0") == "1" and self.mode != _native.MODE_DIRECT
@@ -107,6 +159,7 @@ class DeviceShardEngine(object):
         self._mapping = None
         self._mapping_job = None  # background registration after a cold restore
         self._keepalive = []
+        self._save_bytes = 0
         self.stats = {}
 
     # -- plan -------------------------------------------------------------
@@ -240,7 +293,19 @@ class DeviceShardEngine(object):
             self._stage_host_leaves(host, to_device=True)
             t1 = time.perf_counter()
             staging_ptr = self._staging.data_ptr() if self._staging is not None else None
-            plan.save_async(staging_ptr, addr, self.mode, self.checksum, stream.cuda_stream)
+            if self.tuner is not None:
+                self.mode = self.tuner.mode()
+            try:
+                plan.save_async(staging_ptr, addr, self.mode, self.checksum, stream.cuda_stream)
+            except _native.FcpError:
+                if self.tuner is None or self.mode != _native.MODE_STAGED_KERNEL:
+                    raise
+                # the host pointer is not usable from the device as is: stay
+                # with the copy engine (nothing was launched)
+                self.tuner.kernel_leg_failed()
+                self.mode = _native.MODE_STAGED
+                plan.save_async(staging_ptr, addr, self.mode, self.checksum, stream.cuda_stream)
+            self._save_bytes = total
             self.stats["plan_s"] = t1 - t0
 
     def save_packed_wait(self):
@@ -250,6 +315,11 @@ class DeviceShardEngine(object):
         sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
         self._keepalive = []
         self.stats.update(self._plan.timings())
+        self.stats["save_mode"] = self.mode
+        if self.tuner is not None:
+            self.tuner.report(self.mode, self._save_bytes, self.stats.get("total_ms", 0.0) / 1e3)
+            if self.tuner.settled:
+                self.mode = self.tuner.choice
         self.stats["xxh64"] = self._staged_xxh64() if self.xxh64 else None
         return sums
 

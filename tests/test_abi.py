@@ -69,3 +69,42 @@ def test_bad_geometry_is_rejected():
     import pytest
     with pytest.raises(_native.FcpError):
         _native.finish_checksums(np.zeros(1, dtype=np.uint32), 10, 1000)
+
+
+def test_save_leg_tuner_state_machine():
+    """The run-time choice of the device->host leg (transfer.SaveLegTuner): no
+    GPU needed, it only looks at (mode, bytes, seconds)."""
+    from dlrover_wuqiong_b200 import _native, transfer
+
+    G = 1 << 30
+    CE, K = _native.MODE_STAGED, _native.MODE_STAGED_KERNEL
+    # healthy link: the first save is ignored, the second settles on the copy engine
+    t = transfer.SaveLegTuner()
+    assert t.mode() == CE
+    t.report(CE, 19 * G, 0.9)  # first save of a process: slow, not a sample
+    assert not t.settled and t.mode() == CE
+    t.report(CE, 19 * G, 19 * G / 57e9)
+    assert t.settled and t.choice == CE and t.mode() == CE
+    # copy-engine writes do not scale on this host: try the kernel, keep it if > 10 % faster
+    t = transfer.SaveLegTuner()
+    t.report(CE, 19 * G, 1.0)
+    t.report(CE, 19 * G, 19 * G / 33e9)
+    assert not t.settled and t.mode() == K
+    t.report(K, 19 * G, 19 * G / 51e9)
+    assert t.settled and t.choice == K and t.mode() == K
+    # ... or not
+    t = transfer.SaveLegTuner()
+    t.report(CE, 19 * G, 1.0)
+    t.report(CE, 19 * G, 19 * G / 33e9)
+    t.report(K, 19 * G, 19 * G / 34e9)
+    assert t.settled and t.choice == CE
+    # small saves say nothing about the link; a failing kernel leg ends the probe
+    t = transfer.SaveLegTuner()
+    for _ in range(5):
+        t.report(CE, 100 << 20, 1.0)
+    assert t.state == "warmup"
+    t.report(CE, 2 * G, 1.0)
+    t.report(CE, 2 * G, 1.0)
+    assert t.mode() == K
+    t.kernel_leg_failed()
+    assert t.settled and t.mode() == CE
