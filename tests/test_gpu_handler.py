@@ -295,3 +295,42 @@ def test_raw_persisted_file_restores_in_place_through_the_scatter_kernel(monkeyp
             AsyncCheckpointSaver._saver_instance.close()
             AsyncCheckpointSaver._saver_instance = None
         clear_sock_dir()
+
+
+def test_save_leg_is_probed_and_chosen_at_run_time(monkeypatch):
+    """Force the tuner to distrust the copy engine: the third save must go
+    through the copy kernel, every image must still be the reference's bytes,
+    and the process must settle on one of the two legs."""
+    from dlrover_wuqiong_b200 import transfer
+
+    monkeypatch.delenv("FCP_TRANSFER_MODE", raising=False)
+    monkeypatch.setattr(transfer.SaveLegTuner, "GOOD_GBPS", 1e9)
+    monkeypatch.setattr(transfer.SaveLegTuner, "MIN_BYTES", 1 << 20)
+    torch.manual_seed(5)
+    tensors = {"w%d" % i: torch.randn((1 << 20) + 3 * i, device="cuda") for i in range(24)}
+    sd = dict(tensors)
+    sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=1, paths={})
+    h = SharedMemoryHandler(45, host=True)
+    try:
+        modes = []
+        for step in range(5):
+            with torch.no_grad():
+                tensors["w3"].add_(1.0)
+            meta, total, expect = oracle.pack({k: v for k, v in sd.items()
+                                               if k != DLROVER_CKPT_CONFIG_KEY})
+            h.save_state_dict(sd)
+            modes.append(h._engine.stats["save_mode"])
+            assert bytes(h.shared_memory.buf[:total]) == expect.tobytes(), step
+            sums = h.metadata.get()[FCP_CHECKSUM_KEY]["sums"]
+            assert sums == oracle.chunk_crc32c(expect, _native.DEFAULT_CHUNK_BYTES).tolist()
+        assert modes[:3] == [_native.MODE_STAGED, _native.MODE_STAGED, _native.MODE_STAGED_KERNEL]
+        tuner = h._engine.tuner
+        assert tuner.settled and set(tuner.rates) == {"engine", "kernel"}
+        assert modes[3] == modes[4] == tuner.choice
+        into = {k: torch.zeros_like(v) for k, v in tensors.items()}
+        h.load_state_dict(into=into)
+        for k, v in tensors.items():
+            assert torch.equal(into[k], v)
+    finally:
+        h.unlink()
+        h.close()
