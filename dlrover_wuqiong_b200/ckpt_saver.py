@@ -469,7 +469,11 @@ class SharedMemoryHandler(object):
         """The writer re-creates the segment when the layout changes; a reader
         still mapped to the old one must re-attach."""
         try:
-            return os.stat("/dev/shm/" + self._shm_name).st_size != self.shared_memory.size
+            now = os.stat("/dev/shm/" + self._shm_name)
+            if now.st_size != self.shared_memory.size:
+                return True
+            fd = getattr(self.shared_memory, "_fd", -1)
+            return fd >= 0 and os.fstat(fd).st_ino != now.st_ino
         except OSError:
             return False
 
@@ -969,6 +973,10 @@ class FsdpDcpSaver(CommonDirCheckpointSaver):
         # (the reference calls _dist_make_dir here, whose rmtree lets the
         # shards of one node delete each other's files; SAVER:1181-1185)
         self.storage.safe_makedirs(checkpoint_dir)
+        if handler.shared_memory is None or handler._segment_replaced():
+            # the trainer re-creates the segment when its plan changes size;
+            # a mapping made before that still shows the old image
+            handler.init_shared_memory(create=False)
         assert handler.shared_memory is not None
         self.storage.write(handler.shared_memory.buf, path)
         if self._is_agent_rank_0 and local_shard_id == 0:

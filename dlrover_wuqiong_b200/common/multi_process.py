@@ -327,16 +327,23 @@ class SharedDict(LocalSocketComm):
     def _apply(self, updates):
         """Assign `value` at every `path` (a tuple of keys / list indices) of
         the served dict; all-or-nothing."""
+        if not self._dict:
+            return False  # nothing to patch (e.g. a restarted server): needs a full set
         slots = []
         for path, value in updates:
             node = self._dict
             try:
                 for key in path[:-1]:
-                    node = node[key]
+                    try:
+                        node = node[key]
+                    except TypeError:  # a plain object on the way: by attribute
+                        node = getattr(node, key)
                 if isinstance(node, list):
                     node[path[-1]]  # must exist
+                elif not isinstance(node, dict):
+                    return False
                 slots.append((node, path[-1], value))
-            except (KeyError, IndexError, TypeError):
+            except (KeyError, IndexError, TypeError, AttributeError):
                 return False
         for node, key, value in slots:
             node[key] = value

@@ -37,11 +37,18 @@ class FsdpShardCheckpointer(Checkpointer):
     """
 
     def __init__(self, checkpoint_dir: str, comm_backend="", deletion_strategy=None,
-                 save_timeout=CheckpointConstant.SAVE_TIMEOUT):
+                 save_timeout=CheckpointConstant.SAVE_TIMEOUT, async_save=None):
+        """`async_save` (addition; default from FCP_ASYNC_SAVE): on the GPU
+        path save_checkpoint returns once the shards are snapshotted in HBM
+        staging; the transfer into shm finishes behind the next steps."""
         self.checkpoint_dir = checkpoint_dir
         self.storage = get_checkpoint_storage(deletion_strategy)
         self._engine = FsdpCheckpointEngine(checkpoint_dir, self.storage, comm_backend,
-                                            save_timeout)
+                                            save_timeout, async_save=async_save)
+
+    def wait_latest_checkpoint(self):
+        """Block until the last (async) save is complete in shared memory."""
+        self._engine.wait_async_save()
 
     def save_checkpoint(self, step, model, optimizer, extra_sd={}, path="",
                         storage_type=StorageType.DISK):

@@ -25,6 +25,8 @@ import dataclasses
 import io
 import os
 import pickle
+import threading
+import time
 from dataclasses import dataclass
 from pathlib import Path
 from typing import Any, Dict, List, Union
@@ -43,6 +45,7 @@ from torch.distributed.checkpoint.planner import (
     WriteItemType,
 )
 from torch.distributed.checkpoint.storage import StorageReader, StorageWriter, WriteResult
+from torch.distributed.checkpoint.utils import _DistWrapper
 
 from ..ckpt_saver import (
     DLROVER_CKPT_CONFIG_KEY,
@@ -91,6 +94,30 @@ class _StoragePrefix:
     prefix: str
 
 
+_COMPACT_TAG = "\0fcp_t"
+
+
+def _compact(value):
+    """Non-sharded tensors travel in every rank's meta dict (broadcast from
+    rank 0, then pickled to the agent) on every save; a tensor pickles ~100x
+    slower than its bytes, so they go as (tag, dtype name, shape, bytes)."""
+    if torch.is_tensor(value):
+        t = value.detach().cpu().contiguous()
+        return (_COMPACT_TAG, str(t.dtype).split(".", 1)[1], tuple(t.shape),
+                t.reshape(-1).view(torch.uint8).numpy().tobytes())
+    return value
+
+
+def _expand(value):
+    if isinstance(value, tuple) and len(value) == 4 and value[0] == _COMPACT_TAG:
+        _, dtype_name, shape, raw = value
+        dtype = getattr(torch, dtype_name)
+        if not raw:
+            return torch.empty(shape, dtype=dtype)
+        return torch.frombuffer(bytearray(raw), dtype=dtype).reshape(shape)
+    return value
+
+
 def _item_leaf(data, offset):
     """A plan item as a (tensor, dense meta) leaf of the packed image.
     BYTE_IO payloads become host uint8 tensors."""
@@ -122,6 +149,21 @@ class SharedMemoryWriter(StorageWriter):
         self.shm_handler = shm_handler
         self.metadata: Dict[str, Any] = {}
         self.checksums = None
+        # async saves: write_data returns once the pack kernels are done; the
+        # engine finishes the transfer later (FsdpCheckpointEngine)
+        self.defer_finish = False
+        self.pending_engine = None
+
+    def finish_transfer(self):
+        """Wait for the bytes to be in shm; fills `checksums`."""
+        engine, self.pending_engine = self.pending_engine, None
+        if engine is None:
+            return
+        sums = engine.save_finish()
+        self.shm_handler.last_stats = dict(engine.stats)
+        if sums is not None:
+            from ..transfer import checksums_to_meta
+            self.checksums = checksums_to_meta(sums, engine.chunk_bytes)
 
     # torch >= 2.2 abstract hooks
     def reset(self, checkpoint_id: Union[str, os.PathLike, None] = None) -> None:
@@ -171,11 +213,11 @@ class SharedMemoryWriter(StorageWriter):
             if engine is not None:
                 engine.save_begin(leaves, offset, h.shared_memory.buf,
                                   ready=getattr(h.shared_memory, "wait_populated", None))
-                sums = engine.save_finish()
-                h.last_stats = dict(engine.stats)
-                if sums is not None:
-                    from ..transfer import checksums_to_meta
-                    self.checksums = checksums_to_meta(sums, engine.chunk_bytes)
+                self.pending_engine = engine
+                if self.defer_finish:
+                    engine.save_packed_wait()  # sources are free; DMA goes on
+                else:
+                    self.finish_transfer()
             else:
                 _host_write_leaves(leaves, h.shared_memory.buf)
         self.metadata["no_shard_data"] = no_shard_data
@@ -229,7 +271,7 @@ class SharedMemoryReader(StorageReader):
         return global_plan
 
     def _no_shard_bytes(self, fqn):
-        data = self.no_shard_data[fqn]
+        data = _expand(self.no_shard_data[fqn])
         if isinstance(data, io.BytesIO):
             bytes_io = data
         else:
@@ -257,8 +299,10 @@ class SharedMemoryReader(StorageReader):
                 continue
             target = planner.resolve_tensor(item).detach()
             if replicated:
-                tensor = torch.load(self._no_shard_bytes(item.storage_index.fqn),
-                                    weights_only=False)
+                tensor = _expand(self.no_shard_data[item.storage_index.fqn])
+                if not torch.is_tensor(tensor):  # stored as a pickled object
+                    tensor = torch.load(self._no_shard_bytes(item.storage_index.fqn),
+                                        weights_only=False)
                 tensor = narrow_tensor_by_index(tensor, item.storage_offsets, item.lengths)
                 assert target.size() == tensor.size(), \
                     "req %s mismatch sizes %s vs %s" % (item.storage_index, target.size(),
@@ -399,15 +443,50 @@ class FileReader(StorageReader):
         return global_plan
 
 
+def _same_plan(a: SavePlan, b: SavePlan) -> bool:
+    """Two local plans describe the same items (name, kind, slice of the
+    global tensor, dtype), i.e. the global plan built from them is the same."""
+    if len(a.items) != len(b.items):
+        return False
+    for x, y in zip(a.items, b.items):
+        if x.type != y.type or x.index != y.index:
+            return False
+        tx, ty = x.tensor_data, y.tensor_data
+        if (tx is None) != (ty is None):
+            return False
+        if tx is not None:
+            if tx.size != ty.size or tx.properties.dtype != ty.properties.dtype:
+                return False
+            cx, cy = tx.chunk, ty.chunk
+            if (cx is None) != (cy is None):
+                return False
+            if cx is not None and (cx.offsets != cy.offsets or cx.sizes != cy.sizes):
+                return False
+    return True
+
+
+@dataclass
+class _PlanCache:
+    """What one planned save leaves behind for the next one."""
+    local_plan: SavePlan      # this rank's proposal
+    central_plan: SavePlan    # what the coordinator sent back (items + file prefix)
+    results: List[WriteResult]  # this rank's write results (index, offset, length)
+
+
 class FsdpCheckpointEngine(CheckpointEngine):
     """Saves / loads the FSDP distributed checkpoint of this rank to / from
     its shm segment; every local rank is a shard."""
 
     def __init__(self, checkpoint_dir: str, storage, comm_backend="",
-                 save_timeout=CheckpointConstant.SAVE_TIMEOUT):
-        super().__init__(checkpoint_dir, storage, comm_backend, save_timeout)
+                 save_timeout=CheckpointConstant.SAVE_TIMEOUT, async_save=None):
+        super().__init__(checkpoint_dir, storage, comm_backend, save_timeout,
+                         async_save=async_save)
         self._shm_writer = SharedMemoryWriter(shm_handler=self._shm_handler)
         self._shm_reader = SharedMemoryReader(self._shm_handler)
+        self._plan_cache = None
+        self.last_save_planned = True
+        self._moved_items = {}
+        self._meta_delta_ok = False  # the agent's copy of the meta, see _publish_meta
 
     def get_saving_ranks(self):
         return None  # all ranks
@@ -417,6 +496,8 @@ class FsdpCheckpointEngine(CheckpointEngine):
         """`paths["model_states"]` is the checkpoint *directory* of this step."""
         if self._local_rank != self.local_shard_id:
             return False
+        t_begin = time.perf_counter()
+        self.wait_async_save()
         acquired = self._shm_lock.acquire(blocking=False)
         all_rank_ready = check_all_rank_ready(self._saver_group, acquired)
         if not all_rank_ready:
@@ -431,30 +512,159 @@ class FsdpCheckpointEngine(CheckpointEngine):
         meta_now = self._shm_handler.metadata.get(local=True)
         if meta_now and DLROVER_CKPT_CONFIG_KEY in meta_now:
             meta_now[DLROVER_CKPT_CONFIG_KEY].writing_shm = True
-            self._shm_handler.metadata.set(meta_now)
-        # the reference relies on torch-2.0 planning: replicated items are
-        # written by the lowest rank only
-        planner = dist_cp.DefaultSavePlanner(dedup_save_to_lowest_rank=True)
-        dist_cp.save(state_dict, storage_writer=self._shm_writer, planner=planner,
-                     no_dist=not dist.is_initialized())
-        if dist.is_initialized():
-            # rank 0's DCP metadata + non-sharded data go to every rank's meta
-            box = [self._shm_writer.metadata]
-            dist.broadcast_object_list(box, src=0)
-            self._shm_writer.metadata = box[0]
+            if not (self._meta_delta_ok and self._shm_handler.metadata.update(
+                    [((DLROVER_CKPT_CONFIG_KEY,), meta_now[DLROVER_CKPT_CONFIG_KEY])])):
+                self._meta_delta_ok = False
+                self._shm_handler.metadata.set(meta_now)
+        self._shm_writer.defer_finish = self._async_save
+        self._dcp_save(state_dict)
         model_sd_name = CheckpointConstant.MODEL_STATES_NAME
         conf.paths = {model_sd_name: os.path.join(paths[model_sd_name],
                                                   self._shm_writer.file_name)}
         meta_dict = {DLROVER_CKPT_CONFIG_KEY: conf}
         meta_dict.update(self._shm_writer.metadata)
-        if self._shm_writer.checksums is not None:
-            meta_dict[FCP_CHECKSUM_KEY] = self._shm_writer.checksums
-        conf.writing_shm = False
-        self._shm_handler.metadata.set(meta_dict)
-        if acquired:
-            self._shm_lock.release()
+
+        def finish():
+            try:
+                self._shm_writer.finish_transfer()
+                if self._shm_writer.checksums is not None:
+                    meta_dict[FCP_CHECKSUM_KEY] = self._shm_writer.checksums
+                conf.writing_shm = False
+                self._publish_meta(meta_dict)
+            finally:
+                if acquired:
+                    self._shm_lock.release()
+
         self._cached_step = conf.step
+        if self._shm_writer.pending_engine is not None:
+            # async save: the tensors are snapshotted in HBM staging, training
+            # may go on; the lock and writing_shm=True are held until the image
+            # and its checksums are in shm
+            self._finisher = threading.Thread(target=finish, name="fcp-finisher", daemon=True)
+            self._finisher.start()
+        else:
+            finish()
+        self.last_save_to_memory_s = time.perf_counter() - t_begin  # what training waited for
         return True
+
+    def _publish_meta(self, meta_dict):
+        """Make the agent's copy of the meta equal `meta_dict`.  After a
+        cached-plan save only the config, the checksums, the non-sharded data
+        and the places of moved items differ from what the agent holds, so
+        only those travel (the DCP metadata of a 1000-item plan pickles to
+        ~4000 objects); anything else, or an agent that cannot apply the
+        patch, gets the whole dict."""
+        shared = self._shm_handler.metadata
+        if self._meta_delta_ok and not self.last_save_planned \
+                and os.getenv("FCP_META_DELTA", "1") == "1":
+            updates = [((key,), meta_dict[key]) for key in
+                       (DLROVER_CKPT_CONFIG_KEY, FCP_CHECKSUM_KEY, "no_shard_data")
+                       if key in meta_dict]
+            updates += [(("dcp_metadata", "storage_data", index), info)
+                        for index, info in self._moved_items.items()]
+            try:
+                if shared.update(updates):
+                    local = shared.get(local=True)
+                    for key, value in meta_dict.items():
+                        local[key] = value
+                    return
+            except Exception as e:  # noqa: BLE001 - fall back to the full set
+                logger.debug("meta update failed (%s); sending the whole meta", e)
+        shared.set(meta_dict)
+        self._meta_delta_ok = True
+
+    def _dcp_save(self, state_dict):
+        """What ``dist_cp.save(state_dict, storage_writer=self._shm_writer)``
+        does (FSDPE:473-476), spelled out so that the planning round trips can
+        be skipped when nothing about the layout changed.
+
+        Planned save (first save, or some rank's local plan differs from its
+        last one): local plans gathered on rank 0, global plan scattered back,
+        bytes written, write results gathered, metadata built by rank 0 — the
+        torch sequence with its three object collectives — then rank 0's DCP
+        metadata and non-sharded data are broadcast so every rank's meta is
+        self-sufficient for a restore (FSDPE:98-102,481-483).
+
+        Cached save (every rank reports an unchanged local plan in one 4-byte
+        vote): the previous central plan is reused as is — its items name
+        tensors, they do not hold them — and so is the metadata; rank 0 only
+        re-derives the offsets of its own items (pickled non-tensor items may
+        change length) and broadcasts that patch with the non-sharded data.
+        One small object collective instead of four large ones."""
+        writer = self._shm_writer
+        use_dist = dist.is_initialized()
+        coordinator = not use_dist or dist.get_rank() == 0
+        # the reference relies on torch-2.0 planning: replicated items are
+        # written by the lowest rank only (SURVEY §8c)
+        planner = dist_cp.DefaultSavePlanner(dedup_save_to_lowest_rank=True)
+        planner.set_up_planner(state_dict=state_dict, storage_meta=writer.storage_meta(),
+                               is_coordinator=coordinator)
+        writer.set_up_storage_writer(coordinator)
+        local_plan = writer.prepare_local_plan(planner.create_local_plan())
+        cache = self._plan_cache
+        unchanged = (cache is not None and _same_plan(local_plan, cache.local_plan)
+                     and "dcp_metadata" in writer.metadata)
+        if unchanged and not coordinator and any(
+                i.type == WriteItemType.BYTE_IO for i in cache.central_plan.items):
+            # this rank writes pickled items whose lengths may move, and only
+            # rank 0 re-derives offsets on the cached path
+            unchanged = False
+        if os.getenv("FCP_DCP_PLAN_CACHE", "1") != "1":
+            unchanged = False
+        if check_all_rank_ready(self._saver_group, unchanged):
+            self._dcp_save_cached(planner, cache, coordinator, use_dist)
+            self.last_save_planned = False
+            return
+        self.last_save_planned = True
+        self._plan_cache = None
+        self._moved_items = {}
+        distw = _DistWrapper(None, use_dist, 0)
+        box = {}
+
+        def global_step(all_local_plans):
+            all_local_plans, box["metadata"] = planner.create_global_plan(all_local_plans)
+            return writer.prepare_global_plan(all_local_plans)
+
+        central_plan = distw.reduce_scatter("plan", lambda: local_plan, global_step)
+        results = []
+
+        def write_data():
+            results.extend(writer.write_data(planner.finish_plan(central_plan), planner).value())
+            return results
+
+        def finish_checkpoint(all_results):
+            writer.finish(metadata=box["metadata"], results=all_results)
+            return box["metadata"]
+
+        distw.all_reduce("write", write_data, finish_checkpoint)
+        writer.metadata["no_shard_data"] = {
+            k: _compact(v) for k, v in writer.metadata["no_shard_data"].items()}
+        if use_dist:
+            # rank 0's DCP metadata + non-sharded data go to every rank's meta
+            out = [writer.metadata]
+            dist.broadcast_object_list(out, src=0)
+            writer.metadata = out[0]
+        self._plan_cache = _PlanCache(local_plan, central_plan, list(results))
+
+    def _dcp_save_cached(self, planner, cache, coordinator, use_dist):
+        writer = self._shm_writer
+        results = writer.write_data(planner.finish_plan(cache.central_plan), planner).value()
+        patch = None
+        if coordinator:
+            # only the items whose place moved (a pickled item changed length)
+            moved = {wr.index: wr.storage_data for wr, old in zip(results, cache.results)
+                     if wr.storage_data != old.storage_data}
+            patch = (moved,
+                     {k: _compact(v) for k, v in writer.metadata["no_shard_data"].items()})
+        if use_dist:
+            out = [patch]
+            dist.broadcast_object_list(out, src=0)
+            patch = out[0]
+        dcp_metadata = writer.metadata["dcp_metadata"]  # kept from the planned save
+        dcp_metadata.storage_data.update(patch[0])
+        self._moved_items = patch[0]
+        writer.metadata = {"dcp_metadata": dcp_metadata, "no_shard_data": patch[1]}
+        cache.results = list(results)
 
     def save_to_storage(self, step, state_dict, paths: Dict[str, str]):
         succeed = True
@@ -481,6 +691,7 @@ class FsdpCheckpointEngine(CheckpointEngine):
         """A StorageReader: over shm if it holds a checkpoint all ranks agree
         on, else over the files at `resume_path` / the tracked step; None if
         there is nothing to load."""
+        self.wait_async_save()
         config = self._shm_handler.get_checkpoint_config(CheckpointConfig())
         passed = verify_all_rank_step_consistent(self._saver_group, config.step)
         if passed and not self._shm_handler.no_checkpint_state():

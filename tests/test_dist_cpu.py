@@ -213,6 +213,7 @@ def fsdp_case(rank, world, tmpdir):
                 assert torch.equal(v, opt_before[i][k]), (i, k)
     # DISK: every rank's segment is written raw, node 0 adds .metadata + tracker
     ckpt.save_checkpoint(6, model, opt, {"step": 6}, storage_type=StorageType.DISK)
+    assert ckpt._engine.last_save_planned is True  # "epoch" is gone: the local plans changed
     if rank == 0:
         d = os.path.join(tmpdir, "6")
         assert _wait_for(lambda: os.path.isdir(d) and sorted(os.listdir(d)) ==
@@ -232,6 +233,72 @@ def fsdp_case(rank, world, tmpdir):
     extra = ckpt.load_checkpoint(model, opt)
     assert extra["step"] == 6
     for a, b in zip(flat_before, model.parameters()):
+        assert torch.equal(a, b.detach())
+    # cached plan with new values: train on, save (the pickled `step` grows from
+    # 1 to 3 digits+, so rank 0's item offsets move), wreck, restore from memory
+    opt.zero_grad()
+    model(torch.randint(0, cfg["vocab"], (2, cfg["block"]))).sum().backward()
+    opt.step()
+    flat_now = [p.detach().clone() for p in model.parameters()]
+    opt_now = {i: {k: (v.clone() if torch.is_tensor(v) else v) for k, v in s.items()}
+               for i, s in enumerate(opt.state.values())}
+    assert any(not torch.equal(a, b) for a, b in zip(flat_before, flat_now))
+    assert ckpt.save_checkpoint(70000, model, opt, {"step": 70000},
+                                storage_type=StorageType.MEMORY)
+    assert ckpt._engine.last_save_planned is False
+    meta = handler.metadata.get()
+    mine = sorted((i for i in meta["dcp_metadata"].storage_data.values()
+                   if i.relative_path == "__%d_0.distcp" % rank), key=lambda i: i.offset)
+    for a, b in zip(mine, mine[1:]):
+        assert a.offset + a.length == b.offset
+    assert mine[-1].offset + mine[-1].length == handler.shared_memory.size
+    with torch.no_grad():
+        for p in model.parameters():
+            p.zero_()
+    for s in opt.state.values():
+        for v in s.values():
+            if torch.is_tensor(v):
+                v.zero_()
+    extra = ckpt.load_checkpoint(model, opt)
+    assert extra["step"] == 70000
+    for a, b in zip(flat_now, model.parameters()):
+        assert torch.equal(a, b.detach())
+    for i, s in enumerate(opt.state.values()):
+        for k, v in s.items():
+            if torch.is_tensor(v):
+                assert torch.equal(v, opt_now[i][k]), (i, k)
+    # a new key changes the local plans: planned again, and restorable
+    assert ckpt.save_checkpoint(70001, model, opt, {"step": 70001, "epoch": 4},
+                                storage_type=StorageType.MEMORY)
+    assert ckpt._engine.last_save_planned is True
+    with torch.no_grad():
+        for p in model.parameters():
+            p.zero_()
+    extra = ckpt.load_checkpoint(model, opt)
+    assert extra["step"] == 70001
+    for a, b in zip(flat_now, model.parameters()):
+        assert torch.equal(a, b.detach())
+    # cached plan + patched meta all the way to storage: what the agent persists
+    # must be a loadable DCP checkpoint of the latest values
+    ckpt.save_checkpoint(70002, model, opt, {"step": 70002, "epoch": 5},
+                         storage_type=StorageType.DISK)
+    assert ckpt._engine.last_save_planned is False
+    if rank == 0:
+        d = os.path.join(tmpdir, "70002")
+        assert _wait_for(lambda: os.path.isdir(d) and sorted(os.listdir(d)) ==
+                         [".metadata", "__0_0.distcp", "__1_0.distcp"])
+        tracker = os.path.join(tmpdir, CheckpointConstant.TRACER_FILE_NAME)
+        assert _wait_for(lambda: os.path.exists(tracker) and open(tracker).read() == "70002")
+    dist.barrier()
+    handler.metadata.set({})
+    dist.barrier()
+    with torch.no_grad():
+        for p in model.parameters():
+            p.zero_()
+    assert isinstance(ckpt._engine.load(), FileReader)
+    extra = ckpt.load_checkpoint(model, opt)
+    assert extra["step"] == 70002, extra
+    for a, b in zip(flat_now, model.parameters()):
         assert torch.equal(a, b.detach())
     ckpt.close()
 

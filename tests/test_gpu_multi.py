@@ -150,6 +150,143 @@ def _worker(rank, world, port, run_id, tmpdir, errq):
         raise
 
 
+def _fsdp_worker(rank, world, port, run_id, tmpdir, errq):
+    """FSDP sharded checkpoint on GPUs: planned save, cached-plan saves (sync
+    and async), restore through the scatter kernel; rank 0 records how long
+    save_to_memory blocks."""
+    try:
+        import json
+        import time
+        if ROOT not in sys.path:
+            sys.path.insert(0, ROOT)
+        os.environ.update({
+            "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank),
+            "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank), "LOCAL_WORLD_SIZE": str(world),
+            "NODE_NUM": "1", "NODE_RANK": "0", "ROLE_NAME": "dlrover-trainer",
+            "TORCHELASTIC_RUN_ID": run_id, "DLROVER_LOG_LEVEL": "WARNING"})
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", rank))
+        from torch.distributed.fsdp import FullyShardedDataParallel as FSDP
+        from dlrover_wuqiong_b200.ckpt_saver import AsyncCheckpointSaver
+        from dlrover_wuqiong_b200.flash_checkpoint.fsdp import FsdpCheckpointer, StorageType
+        if rank == 0:
+            AsyncCheckpointSaver.start_async_saving_ckpt()
+        torch.manual_seed(9)
+        width, layers = 1024, 24
+        blocks = []
+        for _ in range(layers):
+            blocks += [nn.LayerNorm(width), nn.Linear(width, 4 * width), nn.GELU(),
+                       nn.Linear(4 * width, width)]
+        model = FSDP(nn.Sequential(*blocks).cuda(), device_id=torch.device("cuda", rank))
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-4)
+
+        def train_step():
+            opt.zero_grad()
+            model(torch.randn(2, width, device="cuda")).square().mean().backward()
+            opt.step()
+
+        def snapshot():
+            return ([p.detach().clone() for p in model.parameters()],
+                    {i: {k: v.clone() for k, v in st.items() if torch.is_tensor(v)}
+                     for i, st in enumerate(opt.state.values())})
+
+        def wreck():
+            with torch.no_grad():
+                for p in model.parameters():
+                    p.zero_()
+            for st in opt.state.values():
+                for v in st.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+
+        def check(snap):
+            for a, b in zip(snap[0], model.parameters()):
+                assert torch.equal(a, b.detach())
+            for i, st in enumerate(opt.state.values()):
+                for k, v in st.items():
+                    if torch.is_tensor(v):
+                        assert torch.equal(v, snap[1][i][k]), (i, k)
+
+        timings = []
+
+        def timed_save(ckpt, step):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            assert ckpt.save_checkpoint(step, model, opt, {"step": step},
+                                        storage_type=StorageType.MEMORY)
+            dt = time.perf_counter() - t0
+            eng = ckpt._engine
+            timings.append({"step": step, "s": dt, "planned": eng.last_save_planned,
+                            "async": eng._async_save,
+                            "save_to_memory_s": getattr(eng, "last_save_to_memory_s", None)})
+
+        train_step()
+        for async_save in (False, True):
+            ckpt = FsdpCheckpointer(os.path.join(tmpdir, "a%d" % async_save), async_save=async_save)
+            base = 100 if async_save else 0
+            timed_save(ckpt, base + 1)
+            assert ckpt._engine.last_save_planned is True
+            for k in (2, 3, 4):
+                train_step()
+                snap = snapshot()
+                timed_save(ckpt, base + k)
+                assert ckpt._engine.last_save_planned is False
+                if async_save:
+                    train_step()  # the live tensors move on while the DMA runs
+                    ckpt.wait_latest_checkpoint()
+            shard_bytes = ckpt._engine._shm_handler.shared_memory.size
+            wreck()
+            extra = ckpt.load_checkpoint(model, opt)
+            assert extra["step"] == base + 4
+            check(snap)
+            ckpt.close()
+        if rank == 0:
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", "fsdp_blocking.json"), "w") as f:
+                json.dump({"world": world, "shard_bytes_rank0": shard_bytes,
+                           "what": "FsdpCheckpointer.save_checkpoint(MEMORY) wall time incl. "
+                                   "FSDP state-dict assembly", "saves": timings}, f, indent=1)
+        dist.barrier()
+        if rank == 0:
+            saver = AsyncCheckpointSaver.get_ckpt_saver()
+            if saver:
+                saver.close()
+        dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        errq.put("rank %d:\n%s" % (rank, traceback.format_exc()))
+        raise
+
+
+def _run_two_ranks(worker, tag):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    ctx = mp.get_context("spawn")
+    errq = ctx.SimpleQueue()
+    port, run_id = _free_port(), "fcp_gpu2_%s_%d" % (tag, os.getpid())
+    with tempfile.TemporaryDirectory() as tmpdir:
+        procs = [ctx.Process(target=worker, args=(r, 2, port, run_id, tmpdir, errq))
+                 for r in range(2)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(200)
+        alive = [p for p in procs if p.is_alive()]
+        for p in alive:
+            p.kill()
+        errors = []
+        while not errq.empty():
+            errors.append(errq.get())
+        assert not alive, "workers hung"
+        assert not errors and all(p.exitcode == 0 for p in procs), "\n".join(errors)
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_fsdp_sharded_cached_plan_and_async():
+    _run_two_ranks(_fsdp_worker, "fsdp")
+
+
 @pytest.mark.timeout(300)
 def test_two_rank_nccl_save_restore_and_peer_recovery():
     if torch.cuda.device_count() < 2:
