@@ -14,7 +14,11 @@ import torch.distributed.checkpoint as dist_cp
 from torch.distributed.checkpoint.optimizer import load_sharded_optimizer_state_dict
 from torch.distributed.fsdp import FullStateDictConfig
 from torch.distributed.fsdp import FullyShardedDataParallel as FSDP
-from torch.distributed.fsdp import StateDictType
+from torch.distributed.fsdp import (
+    ShardedOptimStateDictConfig,
+    ShardedStateDictConfig,
+    StateDictType,
+)
 from torch.distributed.fsdp.api import FullOptimStateDictConfig
 
 from ..common.constants import CheckpointConstant
@@ -62,7 +66,7 @@ class FsdpShardCheckpointer(Checkpointer):
                 (default ``<checkpoint_dir>/<step>``).
             storage_type: StorageType.MEMORY or StorageType.DISK.
         """
-        with FSDP.state_dict_type(model, StateDictType.SHARDED_STATE_DICT):
+        with self._sharded_state(model):
             state_dict = {"model": model.state_dict(),
                           "optim": FSDP.optim_state_dict(model, optimizer)}
             state_dict.update(extra_sd)
@@ -76,6 +80,20 @@ class FsdpShardCheckpointer(Checkpointer):
                 # MEMORY save of the same step ran first; fsdp.py:114)
                 return self._engine.save_to_storage(step, state_dict, paths)
             raise ValueError("No support storage type %s" % storage_type)
+
+    @staticmethod
+    def _sharded_state(model):
+        """SHARDED_STATE_DICT as the reference sets it (fsdp.py:100-103), except
+        that a model living on a GPU keeps its optimizer shards there: torch's
+        default offloads them to the host with one pageable copy per tensor,
+        and the pack kernel would have to bring them back."""
+        on_gpu = any(p.is_cuda for p in model.parameters())
+        if not on_gpu:
+            return FSDP.state_dict_type(model, StateDictType.SHARDED_STATE_DICT)
+        return FSDP.state_dict_type(
+            model, StateDictType.SHARDED_STATE_DICT,
+            state_dict_config=ShardedStateDictConfig(offload_to_cpu=False),
+            optim_state_dict_config=ShardedOptimStateDictConfig(offload_to_cpu=False))
 
     def load_checkpoint(self, model, optimizer, resume_path=""):
         with FSDP.state_dict_type(model, StateDictType.SHARDED_STATE_DICT):

@@ -25,7 +25,13 @@ def worker(rank, world, port, run_id, n_layer, width, tmpdir):
         "GROUP_RANK": "0", "GROUP_WORLD_SIZE": "1", "NODE_NUM": "1", "NODE_RANK": "0",
         "ROLE_NAME": "dlrover-trainer", "TORCHELASTIC_RUN_ID": run_id,
         "DLROVER_LOG_LEVEL": "WARNING"})
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cuda = os.getenv("FSDP_PROBE_CUDA") == "1"
+    if cuda:
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", rank))
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
     from torch.distributed.fsdp import FullyShardedDataParallel as FSDP
     from torch.distributed.fsdp import StateDictType
     from test_dist_cpu import TinyGPT
@@ -35,19 +41,31 @@ def worker(rank, world, port, run_id, n_layer, width, tmpdir):
     if rank == 0:
         AsyncCheckpointSaver.start_async_saving_ckpt()
     torch.manual_seed(3)
-    model = FSDP(TinyGPT(n_layer=n_layer, e=width, vocab=1001, block=16),
-                 device_id=torch.device("cpu"))
-    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
-    model(torch.randint(0, 1001, (2, 16))).sum().backward()
+    if cuda:
+        import torch.nn as nn
+        blocks = []
+        for _ in range(n_layer):
+            blocks += [nn.LayerNorm(width), nn.Linear(width, 4 * width), nn.GELU(),
+                       nn.Linear(4 * width, width)]
+        model = FSDP(nn.Sequential(*blocks).cuda(), device_id=torch.device("cuda", rank))
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-4)
+        model(torch.randn(2, width, device="cuda")).square().mean().backward()
+    else:
+        model = FSDP(TinyGPT(n_layer=n_layer, e=width, vocab=1001, block=16),
+                     device_id=torch.device("cpu"))
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+        model(torch.randint(0, 1001, (2, 16))).sum().backward()
     opt.step()
-    ckpt = FsdpCheckpointer(tmpdir)
+    ckpt = FsdpCheckpointer(tmpdir, async_save=os.getenv("FSDP_PROBE_ASYNC") == "1")
     eng = ckpt._engine
     paths = {CheckpointConstant.MODEL_STATES_NAME: os.path.join(tmpdir, "x")}
     rows = []
     for step in range(1, 7):
+        if cuda:
+            torch.cuda.synchronize()
         dist.barrier()
         t0 = time.perf_counter()
-        with FSDP.state_dict_type(model, StateDictType.SHARDED_STATE_DICT):
+        with FsdpCheckpointer._sharded_state(model):
             sd = {"model": model.state_dict(), "optim": FSDP.optim_state_dict(model, opt), "step": step}
         t1 = time.perf_counter()
         prof = cProfile.Profile() if (rank == 0 and step == 5) else None
@@ -57,8 +75,8 @@ def worker(rank, world, port, run_id, n_layer, width, tmpdir):
         if prof:
             prof.disable()
             s = io.StringIO()
-            pstats.Stats(prof, stream=s).sort_stats("cumulative").print_stats(28)
-            print(s.getvalue()[:6000])
+            pstats.Stats(prof, stream=s).sort_stats("cumulative").print_stats(45)
+            print(s.getvalue()[:9000])
         t2 = time.perf_counter()
         assert ok
         rows.append((t1 - t0, t2 - t1, eng.last_save_planned))
