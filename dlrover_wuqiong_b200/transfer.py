@@ -89,6 +89,17 @@ def buffer_address(buf):
 REGISTER_PIECE_BYTES = 64 << 20
 
 
+def _memmove_all(jobs, workers=4, parallel_above=64 << 20):
+    """jobs: [(dst address, src address, nbytes)], disjoint."""
+    if sum(j[2] for j in jobs) < parallel_above or len(jobs) < 2:
+        for dst, src, n in jobs:
+            ctypes.memmove(dst, src, n)
+        return
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(workers) as pool:
+        list(pool.map(lambda j: ctypes.memmove(j[0], j[1], j[2]), jobs))
+
+
 class HostMapping(object):
     """cudaHostRegister'ed view of the shm segment.
 
@@ -199,22 +210,36 @@ class DeviceShardEngine(object):
             return
         n = sum(lf.nbytes for lf in host)
         pin = self._arena_pin[:n]
+        base = pin.data_ptr()
+        # plain memmove per leaf (GIL released), a few at a time when there is
+        # a lot to move: torch's copy_ fans every 2 MB copy out over all OpenMP
+        # threads, which crawls (~1 GB/s measured) once several ranks and the
+        # agent share the cores
+        jobs, keep, cursor = [], [], 0
         if to_device:
-            cursor = 0
             for lf in host:
-                src = lf.tensor.detach().contiguous().reshape(-1).view(torch.uint8)
-                pin[cursor:cursor + lf.nbytes].copy_(src)
+                src = lf.tensor.detach()
+                if not src.is_contiguous():
+                    src = src.contiguous()
+                    keep.append(src)
+                jobs.append((base + cursor, src.data_ptr(), lf.nbytes))
                 cursor += lf.nbytes
+            _memmove_all(jobs)
             self._arena_dev[:n].copy_(pin, non_blocking=True)
         else:
             pin.copy_(self._arena_dev[:n], non_blocking=False)
-            cursor = 0
+            strided = []
             for lf in host:
                 t = lf.tensor
-                src = pin[cursor:cursor + lf.nbytes].view(t.dtype).reshape(t.shape)
-                with torch.no_grad():
-                    t.copy_(src)
+                if t.is_contiguous():
+                    jobs.append((t.data_ptr(), base + cursor, lf.nbytes))
+                else:
+                    strided.append((t, cursor))
                 cursor += lf.nbytes
+            _memmove_all(jobs)
+            for t, at in strided:
+                with torch.no_grad():
+                    t.copy_(pin[at:at + t.numel() * t.element_size()].view(t.dtype).reshape(t.shape))
 
     def _ensure_plan(self, ptrs, offs, sizes, total):
         key = (total, tuple(offs), tuple(sizes))
