@@ -896,7 +896,12 @@ int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
   if (n_workers > 32) n_workers = 32;
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
-  const uint64_t slot = 8ull << 20;  // small ring: pinned allocation costs ~0.5 s/GiB
+  // small ring: pinned allocation costs ~0.5 s/GiB and is on the critical
+  // path of the first (cold) restore.  Measured on 16 GB, 8 workers: 1 MiB
+  // slots 32 GB/s, 2 MiB 43, 4 MiB 51, 8 MiB 51, 16 MiB 47 (tools/cold_probe.py)
+  static const uint64_t slot_mb =
+      getenv("FCP_BOUNCE_SLOT_MB") ? strtoull(getenv("FCP_BOUNCE_SLOT_MB"), nullptr, 10) : 4;
+  const uint64_t slot = (slot_mb ? slot_mb : 4) << 20;
   if (!p->ring || p->ring_workers < n_workers || p->ring_slot_bytes != slot) {
     if (p->ring) cudaFreeHost(p->ring);
     p->ring = nullptr;

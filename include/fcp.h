@@ -219,7 +219,7 @@ int fcp_restore(fcp_plan* plan, const void* host_src, void* staging, int mode,
  * registered — the situation of a freshly restarted trainer attaching to the
  * shm segment its predecessor left (SAVER:305-306).  Pinning 19 GB takes
  * ~1.6 s (cudaHostRegister does not parallelise), so instead `n_workers` host
- * threads (<= 0: pick from the core count) copy 8 MiB slices of the image
+ * threads (<= 0: pick from the core count) copy 4 MiB slices of the image
  * into a small pinned ring owned by the plan and DMA them from there;
  * the scatter kernel then verifies and unpacks the staged image.
  * Synchronous.                                                              */
