@@ -82,13 +82,30 @@ __device__ __forceinline__ W8 load_packed(const uint8_t* packed, uint64_t o,
 }
 
 // bytes [from, from+n) of w to consecutive addresses starting at t
-__device__ __noinline__ void store_some_bytes(uintptr_t t, const W8& w, int from,
-                                              int n) {
+// Bytes [from, from+n) of a word, stored one by one at t.  Cold (twice per
+// misaligned region).  The word comes as eight scalars on purpose: a
+// `const W8&` parameter made the caller keep its W8s in local memory for the
+// whole loop (two 32-byte local stores per payload word, ~15 % of the kernel).
+__device__ __noinline__ void store_some_bytes_regs(uintptr_t t, uint32_t w0, uint32_t w1,
+                                                   uint32_t w2, uint32_t w3, uint32_t w4,
+                                                   uint32_t w5, uint32_t w6, uint32_t w7,
+                                                   int from, int n) {
+  uint8_t* out = reinterpret_cast<uint8_t*>(t);
 #pragma unroll
-  for (int b = 0; b < kWordBytes; ++b)
-    if (b >= from && b < from + n)
-      reinterpret_cast<uint8_t*>(t)[b - from] =
-          static_cast<uint8_t>(w.v[b >> 2] >> ((b & 3) * 8));
+  for (int i = 0; i < 8; ++i) {
+    const uint32_t w = i == 0 ? w0 : i == 1 ? w1 : i == 2 ? w2 : i == 3 ? w3
+                     : i == 4 ? w4 : i == 5 ? w5 : i == 6 ? w6 : w7;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int b = i * 4 + j;
+      if (b >= from && b < from + n) out[b - from] = static_cast<uint8_t>(w >> (j * 8));
+    }
+  }
+}
+
+__device__ __forceinline__ void store_some_bytes(uintptr_t t, const W8& w, int from, int n) {
+  store_some_bytes_regs(t, w.v[0], w.v[1], w.v[2], w.v[3], w.v[4], w.v[5], w.v[6], w.v[7],
+                        from, n);
 }
 
 // ---------------------------------------------------------------- the kernel
@@ -194,41 +211,40 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
       } else if (!PACK && mis != 0) {
         // target not 32-byte aligned relative to the image: every lane writes
         // the ALIGNED target word that starts inside its packed word, built
-        // from the tail of its own word and the head of its right neighbour's
-        // (one shuffle per register; lane 31 takes lane 0's word of the next
-        // row).  Only the few bytes at the very start and end of the region
-        // go out as byte stores.
+        // from the tail of its own word and the head of the next packed word
+        // (a second aligned load; it is the right neighbour's own word, so an
+        // L1 hit — cheaper than passing eight registers through shuffles).
+        // Only the few bytes at the very start and end of the region go out
+        // as byte stores.
         const uint32_t keep = 32u - mis;        // bytes of my word before the aligned word
         const uintptr_t tw = t0 + keep;         // my aligned target word, row 0
         const uintptr_t src = reinterpret_cast<uintptr_t>(p0);
 #pragma unroll 1
-        for (int row = 0; row < kRows; row += kBatch) {
-          if (lane == 0 && pf && row + kBatch < kRows)
-            prefetch_l2(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16);
-          W8 v[kBatch + 1];
+        for (int row = 0; row < kRows; row += 2) {
+          if (lane == 0 && pf && row + 2 < kRows)
+            prefetch_l2(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 48);
+          W8 v[2], hi[2];
 #pragma unroll
-          for (int k = 0; k < kBatch; ++k)
+          for (int k = 0; k < 2; ++k) {
             v[k] = ld32(reinterpret_cast<const void*>(src + (row + k) * kRowBytes));
-          const bool more = row + kBatch < kRows;
-          if (lane == 0 && more)  // first word of the next batch, for lane 31
-            v[kBatch] = ld32(reinterpret_cast<const void*>(src + (row + kBatch) * kRowBytes));
+            // the word after the region's last one may lie outside the image
+            const bool tail = (row + k == kRows - 1) && lane == 31;
+            if (!tail)
+              hi[k] = ld32(reinterpret_cast<const void*>(
+                  src + (row + k) * kRowBytes + kWordBytes));
+            else
+              hi[k] = v[k];  // unused: that lane writes its tail bytewise
+          }
 #pragma unroll
-          for (int k = 0; k < kBatch; ++k) {
-            W8 hi;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const uint32_t give = (lane == 0) ? v[k + 1].v[i] : v[k].v[i];
-              hi.v[i] = __shfl_sync(0xffffffffu, give, (lane + 1) & 31);
-            }
-            const bool last_row = !more && k == kBatch - 1;
+          for (int k = 0; k < 2; ++k) {
             if (row + k == 0 && lane == 0)
               store_some_bytes(t0, v[k], 0, static_cast<int>(keep));
-            if (last_row && lane == 31) {
+            if ((row + k == kRows - 1) && lane == 31) {
               store_some_bytes(tw + (row + k) * kRowBytes, v[k], static_cast<int>(keep),
                                static_cast<int>(mis));
             } else {
               st32(reinterpret_cast<void*>(tw + (row + k) * kRowBytes),
-                   extract32(v[k], hi, keep));
+                   extract32(v[k], hi[k], keep));
             }
             if (CRC) acc = crc_word<REPL, RK>(tb, acc, v[k]);
           }
