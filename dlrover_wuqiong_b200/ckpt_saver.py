@@ -594,14 +594,16 @@ class AsyncCheckpointSaver(metaclass=ABCMeta):
             if cls._saver_instance:
                 cls._saver_instance.close()
             if callable(prev_int):
-                prev_int(signum, frame)
+                # (called by hand with signum=None, Python >= 3.12's default
+                # handler raises TypeError instead of KeyboardInterrupt)
+                prev_int(signal.SIGINT if signum is None else signum, frame)
 
         def on_sigterm(signum, frame):
             if cls._saver_instance:
                 cls._saver_instance.save_shm_to_storage()
                 cls._saver_instance.close()
             if callable(prev_term):
-                prev_term(signum, frame)
+                prev_term(signal.SIGTERM if signum is None else signum, frame)
 
         signal.signal(signal.SIGINT, on_sigint)
         signal.signal(signal.SIGTERM, on_sigterm)

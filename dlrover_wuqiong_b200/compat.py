@@ -17,6 +17,7 @@ _PKG = "dlrover_wuqiong_b200"
 ALIASES = {
     "dlrover.python.common.constants": _PKG + ".common.constants",
     "dlrover.python.common.env_utils": _PKG + ".common.env_utils",
+    "dlrover.python.common.grpc": _PKG + ".common.grpc",
     "dlrover.python.common.log": _PKG + ".common.log",
     "dlrover.python.common.multi_process": _PKG + ".common.multi_process",
     "dlrover.python.common.serialize": _PKG + ".common.serialize",
@@ -73,3 +74,38 @@ def install(force=False):
         setattr(sys.modules[".".join(parts[:-1])], parts[-1], module)
         done.append(alias)
     return done
+
+
+_SHIM = '''"""Stand-in for the reference's top-level package: importing it makes
+``dlrover.python...`` / ``dlrover.trainer...`` resolve to dlrover_wuqiong_b200
+(written by dlrover_wuqiong_b200.compat.write_shim)."""
+import sys
+
+__fcp_alias__ = True
+sys.path.insert(0, %r)
+from dlrover_wuqiong_b200 import compat as _compat  # noqa: E402
+
+_compat.install(force=True)
+'''
+
+
+def write_shim(directory):
+    """Write ``<directory>/dlrover/__init__.py``.  With `directory` on
+    sys.path / PYTHONPATH every process of a job — spawned trainers, the agent
+    that imports the saver class by module path — resolves the reference's
+    import paths to this package without calling install() itself."""
+    import os
+
+    pkg = os.path.join(directory, "dlrover")
+    os.makedirs(pkg, exist_ok=True)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(pkg, "__init__.py"), "w") as f:
+        f.write(_SHIM % root)
+    return pkg
+
+
+if __name__ == "__main__":
+    if len(sys.argv) == 3 and sys.argv[1] == "--write-shim":
+        print(write_shim(sys.argv[2]))
+    else:
+        sys.exit("usage: python -m dlrover_wuqiong_b200.compat --write-shim DIR")

@@ -140,6 +140,55 @@ def _host_write_leaves(leaves, buf):
                              offset=lf.meta.offset).reshape(lf.meta.shape).copy_(lf.tensor)
 
 
+# -- host-side item helpers, same names and results as the reference's
+# (FSDPE:85-155).  The writer below does not go through them on the GPU path
+# (one pack launch moves every item); they serve host-only callers and keep
+# code written against the reference module importable.
+def _tensor_item_size(item) -> int:
+    """Bytes of the tensor a write item describes — of its *global* shape, as
+    the reference computes it (FSDPE:110-117; see the module docstring)."""
+    numel = 1
+    for dim in item.tensor_data.size:
+        numel *= int(dim)
+    return numel * torch.empty((), dtype=item.tensor_data.properties.dtype).element_size()
+
+
+def _get_buffer_size(files, planner: SavePlanner) -> int:
+    """Upper bound of the bytes `files` = [(file name, write item)] need."""
+    total = 0
+    for _, item in files:
+        if item.type == WriteItemType.BYTE_IO:
+            total += planner.resolve_data(item).getbuffer().nbytes
+        else:
+            total += _tensor_item_size(item)
+    return total
+
+
+def _write_item(shm, offset, data, write_item, storage_key):
+    """Put one resolved item at `offset` of `shm`; -> (next offset, WriteResult)."""
+    lf = _item_leaf(data, offset)
+    if lf.nbytes:
+        _host_write_leaves([lf], shm.buf)
+    result = WriteResult(index=write_item.index, size_in_bytes=lf.nbytes,
+                         storage_data=_StorageInfo(storage_key, offset, lf.nbytes))
+    return offset + lf.nbytes, result
+
+
+def _write_memory_from_list(shm, files, planner: SavePlanner):
+    """Write every item of `files` densely in order; -> (write results,
+    {fqn: data} of the non-sharded items)."""
+    results, no_shard_data, offset = [], {}, 0
+    for storage_key, item in files:
+        data = planner.resolve_data(item)
+        if torch.is_tensor(data):
+            data = data.detach()
+        if item.type != WriteItemType.SHARD:
+            no_shard_data[item.index.fqn] = data
+        offset, result = _write_item(shm, offset, data, item, storage_key)
+        results.append(result)
+    return results, no_shard_data
+
+
 class SharedMemoryWriter(StorageWriter):
     """DCP StorageWriter into the shm segment of `shm_handler`."""
 
