@@ -34,6 +34,7 @@ ALIASES = {
     "dlrover.trainer.torch.flash_checkpoint.deepspeed": _PKG + ".flash_checkpoint.deepspeed",
     "dlrover.trainer.torch.flash_checkpoint.deepspeed_engine":
         _PKG + ".flash_checkpoint.deepspeed_engine",
+    "dlrover.trainer.torch.flash_checkpoint.hf_trainer": _PKG + ".flash_checkpoint.hf_trainer",
     "dlrover.trainer.torch.flash_checkpoint.megatron": _PKG + ".flash_checkpoint.megatron",
     "dlrover.trainer.torch.flash_checkpoint.megatron_engine":
         _PKG + ".flash_checkpoint.megatron_engine",
