@@ -171,6 +171,7 @@ class DeviceShardEngine(object):
         self._mapping_job = None  # background registration after a cold restore
         self._keepalive = []
         self._save_bytes = 0
+        self._warned_host_leaves = False
         self.stats = {}
 
     # -- plan -------------------------------------------------------------
@@ -181,6 +182,14 @@ class DeviceShardEngine(object):
         host = [lf for lf in leaves if lf.nbytes and not lf.is_cuda]
         host_bytes = sum(lf.nbytes for lf in host)
         if host_bytes:
+            if host_bytes > (256 << 20) and not self._warned_host_leaves:
+                self._warned_host_leaves = True
+                logger.warning(
+                    "%.1f GB of this state dict lives in host memory; it joins the image through "
+                    "a pinned arena and the GPU (so that one kernel checksums every byte), which "
+                    "costs two extra trips over the host link. Keep large tensors on the GPU "
+                    "while checkpointing (e.g. ShardedOptimStateDictConfig(offload_to_cpu=False)).",
+                    host_bytes / 1e9)
             if self._arena_pin is None or self._arena_pin.numel() < host_bytes:
                 self._arena_pin = torch.empty(host_bytes, dtype=torch.uint8).pin_memory()
                 self._arena_dev = torch.empty(host_bytes, dtype=torch.uint8,
