@@ -161,3 +161,29 @@ def test_third_party_engine_written_against_the_reference_runs_unchanged():
                          env=env, timeout=300)
     assert out.returncode == 0, (out.stdout[-1500:], out.stderr[-3000:])
     assert out.stdout.strip().endswith("ok")
+
+
+def test_shim_package_resolves_the_reference_paths_in_a_fresh_process(tmp_path):
+    """compat.write_shim: a process that never calls install() — a spawned
+    trainer, an agent importing the saver class by module path — gets the
+    aliases by importing `dlrover` from PYTHONPATH."""
+    sys.path.insert(0, ROOT)
+    try:
+        from dlrover_wuqiong_b200 import compat
+        pkg = compat.write_shim(str(tmp_path))
+    finally:
+        sys.path.remove(ROOT)
+    assert os.path.exists(os.path.join(pkg, "__init__.py"))
+    env = dict(os.environ)
+    env["PYTHONPATH"] = str(tmp_path)
+    code = ("import importlib\n"
+            "m = importlib.import_module('dlrover.python.elastic_agent.torch.ckpt_saver')\n"
+            "cls = getattr(m, 'DeepSpeedCheckpointSaver')\n"
+            "from dlrover.trainer.torch.flash_checkpoint.hf_trainer import HfDdpCheckpointer\n"
+            "from dlrover.python.common.grpc import find_free_port\n"
+            "assert cls.__module__ == 'dlrover_wuqiong_b200.ckpt_saver' and find_free_port() > 0\n"
+            "print('ok')\n")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env,
+                         cwd=str(tmp_path), timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout.strip().endswith("ok")
