@@ -334,3 +334,93 @@ def test_save_leg_is_probed_and_chosen_at_run_time(monkeypatch):
     finally:
         h.unlink()
         h.close()
+
+
+def _random_nested(rng, depth=0):
+    """A random nested state dict: dicts / lists as containers, CUDA and host
+    tensors of mixed dtypes (0-dim, empty, strided views, odd sizes), tuples
+    and scalars as opaque leaves — the shapes the reference's traversal meets
+    (SAVER:94-109)."""
+    dtypes = [torch.float32, torch.bfloat16, torch.float16, torch.float64, torch.int64,
+              torch.int32, torch.int16, torch.uint8, torch.bool]
+
+    def tensor():
+        dt = dtypes[int(rng.integers(len(dtypes)))]
+        kind = int(rng.integers(8))
+        if kind == 0:
+            shape = ()
+        elif kind == 1:
+            shape = (0, int(rng.integers(1, 5)))
+        elif kind == 2:
+            shape = (int(rng.integers(1, 40)), int(rng.integers(1, 40)), int(rng.integers(1, 7)))
+        else:
+            shape = (int(rng.integers(1, 30000)),)
+        n = 1
+        for s in shape:
+            n *= s
+        raw = torch.from_numpy(rng.integers(0, 256, max(n, 1) * 8, dtype=np.uint8))
+        if dt == torch.bool:
+            t = (raw[:n] & 1).bool().reshape(shape)
+        else:
+            t = raw[:n * torch.empty((), dtype=dt).element_size()].view(dt).reshape(shape)
+        if dt.is_floating_point:
+            t = torch.nan_to_num(t.float(), nan=1.0, posinf=2.0, neginf=-2.0).to(dt)
+        if int(rng.integers(5)) != 0:
+            t = t.cuda()
+        if len(shape) == 3 and int(rng.integers(2)):
+            t = t.transpose(0, 1)  # strided view: must be linearised row-major
+        return t
+
+    def leaf():
+        k = int(rng.integers(10))
+        if k < 6:
+            return tensor()
+        return [3, 2.5, "s", None, (1, torch.ones(2)), True][int(rng.integers(6))]
+
+    if depth >= 3:
+        return leaf()
+    out = {}
+    for i in range(int(rng.integers(1, 6))):
+        k = int(rng.integers(4))
+        key = ["k%d" % i, i, "layer.%d.weight" % i][int(rng.integers(3))]
+        if k == 0:
+            out[key] = _random_nested(rng, depth + 1)
+        elif k == 1:
+            out[key] = [leaf() if int(rng.integers(3)) else _random_nested(rng, depth + 1)
+                        for _ in range(int(rng.integers(0, 4)))]
+        else:
+            out[key] = leaf()
+    return out
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_nested_state_dicts_match_the_oracle(seed):
+    rng = np.random.default_rng(1000 + seed)
+    sd = {"model_states": _random_nested(rng), "optim_states": _random_nested(rng)}
+    flat, _, total = oracle.flatten(sd)
+    if not any(t.is_cuda and t.numel() for t, _ in flat):
+        sd["model_states"]["force_gpu"] = torch.arange(7, device="cuda", dtype=torch.int16)
+    meta, total, expect = oracle.pack(sd)
+    sd[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig(step=seed + 1, paths={})
+    h = SharedMemoryHandler(50 + seed, host=True)
+    try:
+        h.save_state_dict(sd)
+        assert h.shared_memory.size == total
+        assert bytes(h.shared_memory.buf[:total]) == expect.tobytes()
+        sums = h.metadata.get()[FCP_CHECKSUM_KEY]["sums"]
+        assert sums == oracle.chunk_crc32c(expect, _native.DEFAULT_CHUNK_BYTES).tolist()
+        # reference-style views and a device restore both reproduce the oracle's unpack
+        want = oracle.unpack(meta, expect)
+        got = h.load_state_dict()
+        fresh = h.load_state_dict(device="cuda")
+        fw, _, _ = oracle.flatten(want)
+        for other in (got, fresh):
+            fo, _, _ = oracle.flatten({k: v for k, v in other.items()
+                                       if k != DLROVER_CKPT_CONFIG_KEY})
+            assert len(fo) == len(fw)
+            for (a, _), (b, _) in zip(fw, fo):
+                assert a.dtype == b.dtype
+                assert oracle.tensor_bytes(a).tobytes() == oracle.tensor_bytes(b).tobytes()
+    finally:
+        h.unlink()
+        h.close()
