@@ -7,6 +7,7 @@ This is the layer that replaces the reference's per-tensor
 on restore.  There is no CPU fallback here: CUDA tensors in the state dict
 require libfcp.so and a CUDA device, or an exception is raised.
 """
+import contextlib
 import ctypes
 import os
 import threading
@@ -313,6 +314,13 @@ class DeviceShardEngine(object):
         return addr
 
     # -- save -------------------------------------------------------------
+    @staticmethod
+    def _nvtx(name):
+        """NVTX range around a phase when FCP_NVTX=1 (for nsys timelines)."""
+        if os.getenv("FCP_NVTX", "0") != "1":
+            return contextlib.nullcontext()
+        return torch.cuda.nvtx.range(name)
+
     def save_begin(self, leaves, total, buf, ready=None):
         """Enqueue pack + transfer of the shard into `buf`; returns once the
         work is enqueued.  Call save_packed_wait() before mutating the tensors
@@ -320,11 +328,14 @@ class DeviceShardEngine(object):
         HostMapping.register_all."""
         with torch.cuda.device(self.device):
             t0 = time.perf_counter()
-            ptrs, offs, sizes, host = self._sources(leaves)
-            plan = self._ensure_plan(ptrs, offs, sizes, total)
-            addr = self._ensure_mapping(buf, total, ready)
+            with self._nvtx("fcp.plan"):
+                ptrs, offs, sizes, host = self._sources(leaves)
+                plan = self._ensure_plan(ptrs, offs, sizes, total)
+            with self._nvtx("fcp.pin"):
+                addr = self._ensure_mapping(buf, total, ready)
             stream = torch.cuda.current_stream(self.device)
-            self._stage_host_leaves(host, to_device=True)
+            with self._nvtx("fcp.host_leaves"):
+                self._stage_host_leaves(host, to_device=True)
             t1 = time.perf_counter()
             staging_ptr = self._staging.data_ptr() if self._staging is not None else None
             if self.tuner is not None:
@@ -343,10 +354,12 @@ class DeviceShardEngine(object):
             self.stats["plan_s"] = t1 - t0
 
     def save_packed_wait(self):
-        self._plan.save_packed_wait()
+        with self._nvtx("fcp.pack_wait"):
+            self._plan.save_packed_wait()
 
     def save_finish(self):
-        sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
+        with self._nvtx("fcp.d2h_wait"):
+            sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
         self._keepalive = []
         self.stats.update(self._plan.timings())
         self.stats["save_mode"] = self.mode
@@ -355,6 +368,15 @@ class DeviceShardEngine(object):
             if self.tuner.settled:
                 self.mode = self.tuner.choice
         self.stats["xxh64"] = self._staged_xxh64() if self.xxh64 else None
+        total_ms, kernel_ms = self.stats.get("total_ms", 0.0), self.stats.get("kernel_ms", 0.0)
+        if total_ms > 0 and self._save_bytes:
+            # the reference logs seconds only (FC/engine.py:94-105); rates tell
+            # whether the link or the host is the limit
+            self.stats["save_GBps"] = self._save_bytes / total_ms / 1e6
+            logger.info("flash checkpoint save: %.2f GB in shm after %.1f ms (%.1f GB/s over the "
+                        "host link), tensors free after %.1f ms (pack %.0f GB/s of HBM traffic)",
+                        self._save_bytes / 1e9, total_ms, self.stats["save_GBps"], kernel_ms,
+                        2 * self._save_bytes / kernel_ms / 1e6 if kernel_ms > 0 else 0.0)
         return sums
 
     def _staged_xxh64(self):
@@ -423,6 +445,12 @@ class DeviceShardEngine(object):
             self.stats["restore_prepare_s"] = t_ready - t_begin
             self.stats["restore_move_s"] = t_moved - t_ready
             self.stats["restore_host_leaves_s"] = time.perf_counter() - t_moved
+            if total:
+                wall = time.perf_counter() - t_begin
+                self.stats["restore_GBps"] = total / wall / 1e9
+                logger.info("flash checkpoint restore (%s): %.2f GB into live tensors in %.1f ms "
+                            "(%.1f GB/s)", self.stats["restore_path"], total / 1e9, wall * 1e3,
+                            self.stats["restore_GBps"])
             if expected_xxh64 is not None and self.xxh64:
                 got = self._staged_xxh64()
                 if got != list(expected_xxh64):

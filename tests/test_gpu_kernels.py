@@ -301,3 +301,59 @@ def test_image_beyond_4gib_by_properties():
         crcs.append(np.asarray(p.read_checksums(_stream()), dtype=np.uint32))
         p.close()
     assert np.array_equal(crcs[2], crcs[0] ^ crcs[1] ^ crcs[3])
+
+
+@pytest.mark.parametrize("seed,n,max_elems", [(11, 40, 5000), (12, 300, 900), (13, 6, 3_000_000),
+                                              (14, 1500, 60), (15, 14, 12_000_000)])
+def test_guard_bytes_around_image_and_tensors_stay_intact(seed, n, max_elems):
+    """Own bounds check (compute-sanitizer is not available on this pool):
+    the image sits between two guard pages and every scatter target between
+    two 64-byte guards inside a larger buffer, at odd addresses; after pack
+    and scatter (both kernel shapes, realigning paths included) no guard byte
+    may have changed and nothing but the targets may have been written."""
+    rng = np.random.default_rng(seed)
+    dev = _dev()
+    G = 64
+    flat, bufs, off = [], [], 0
+    for i in range(n):
+        dt = DT[int(rng.integers(len(DT)))]
+        es = torch.empty((), dtype=dt).element_size()
+        numel = int(rng.integers(1, max_elems))
+        nbytes = numel * es
+        lead = G + int(rng.integers(0, 16 // es if es < 16 else 1)) * es  # odd but dtype-aligned
+        buf = torch.full((lead + nbytes + G + 16,), 0xEE, dtype=torch.uint8, device=dev)
+        buf[lead:lead + nbytes] = torch.from_numpy(
+            rng.integers(0, 256, nbytes, dtype=np.uint8)).to(dev)
+        t = buf[lead:lead + nbytes].view(dt)
+        if i % 3 == 0:
+            off += int(rng.integers(1, 9))  # a hole in the image: must stay untouched too
+        flat.append((t, oracle.OMeta((numel,), dt, es, numel, off)))
+        bufs.append((buf, lead, nbytes))
+        off += nbytes
+    total = off
+    plan, keep = _plan_for(flat, total, chunk=65536)
+    if seed == 15:  # large enough for the 1024-thread shape with replicated tables
+        assert total > 148 * 32 * 16384, total
+    page = 4096
+    arena = torch.full((plan.staging_bytes + 2 * page,), 0x77, dtype=torch.uint8, device=dev)
+    image = arena[page:page + plan.staging_bytes]
+    plan.pack(image.data_ptr(), _native.SUM_CRC32C, _stream())
+    torch.cuda.synchronize()
+    assert bool((arena[:page] == 0x77).all()) and bool((arena[page + plan.staging_bytes:] == 0x77).all())
+    sums = plan.read_checksums(_stream())
+    # sources untouched by the pack (guards and payload)
+    snap = [b.clone() for b, _, _ in bufs]
+    # scatter into fresh guarded targets at the same odd addresses
+    targets = []
+    for (buf, lead, nbytes), (t, m) in zip(bufs, flat):
+        tb = torch.full_like(buf, 0xEE)
+        targets.append((tb, tb[lead:lead + nbytes].view(t.dtype)))
+    plan.update_ptrs([v.data_ptr() for _, v in targets])
+    plan.scatter(image.data_ptr(), _native.SUM_CRC32C, _stream())
+    torch.cuda.synchronize()
+    assert plan.read_checksums(_stream()).tolist() == sums.tolist()
+    assert bool((arena[:page] == 0x77).all()) and bool((arena[page + plan.staging_bytes:] == 0x77).all())
+    for (buf, lead, nbytes), s, (tb, _) in zip(bufs, snap, targets):
+        assert torch.equal(buf, s)          # the pack wrote nothing into its sources
+        assert torch.equal(tb, buf), lead   # payload restored, guards still 0xEE
+    plan.close()
