@@ -529,11 +529,20 @@ def run_ours(args, rank, local_rank, world):
 
     # ---- leg 2: `e2e` — DdpCheckpointer.save_checkpoint(MEMORY) + load_checkpoint(into)
     _barrier_sync(device)
+    e2e_prof = None
+    if os.getenv("FCP_PROFILE_E2E") and rank == 0:  # tuning aid: where the host time goes
+        import cProfile
+        e2e_prof = cProfile.Profile()
+        e2e_prof.enable()
     t0 = time.perf_counter()
     for k in range(K):
         e2e_step(100 + k)
     torch.cuda.synchronize(device)
     e2e_s = _dist_max(time.perf_counter() - t0, device)
+    if e2e_prof:
+        import pstats
+        e2e_prof.disable()
+        pstats.Stats(e2e_prof, stream=sys.stderr).sort_stats("tottime").print_stats(30)
     _barrier_sync(device)
 
     # ---- leg 3: training-blocking time of a save through the Python API
