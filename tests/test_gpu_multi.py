@@ -238,7 +238,13 @@ def _fsdp_worker(rank, world, port, run_id, tmpdir, errq):
                     ckpt.wait_latest_checkpoint()
             shard_bytes = ckpt._engine._shm_handler.shared_memory.size
             wreck()
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
             extra = ckpt.load_checkpoint(model, opt)
+            torch.cuda.synchronize()
+            timings.append({"load_checkpoint_s": time.perf_counter() - t0, "async": async_save,
+                            "restore_path": ckpt._engine._shm_handler.last_stats.get("restore_path")})
             assert extra["step"] == base + 4
             check(snap)
             ckpt.close()

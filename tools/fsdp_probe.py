@@ -87,6 +87,27 @@ def worker(rank, world, port, run_id, n_layer, width, tmpdir):
             n_items, h.shared_memory.size / 1e6))
         for i, (a, b, planned) in enumerate(rows, 1):
             print("save %d: state-dict assembly %.1f ms, save_to_memory %.1f ms (%s)" % (i, a * 1e3, b * 1e3, "planned" if planned else "cached plan"))
+    # ---- restore from memory, profiled on rank 0
+    ckpt.wait_latest_checkpoint()
+    for rep in range(2):
+        if cuda:
+            torch.cuda.synchronize()
+        dist.barrier()
+        prof = cProfile.Profile() if (rank == 0 and rep == 1) else None
+        t0 = time.perf_counter()
+        if prof:
+            prof.enable()
+        extra = ckpt.load_checkpoint(model, opt)
+        if cuda:
+            torch.cuda.synchronize()
+        if prof:
+            prof.disable()
+            s = io.StringIO()
+            pstats.Stats(prof, stream=s).sort_stats("cumulative").print_stats(60)
+            print(s.getvalue()[:14000])
+        if rank == 0:
+            print("load %d: load_checkpoint %.1f ms (step %s)" % (
+                rep, (time.perf_counter() - t0) * 1e3, extra.get("step")))
     dist.barrier()
     ckpt.close()
     if rank == 0:
