@@ -453,3 +453,32 @@ def test_shared_memory_is_populated_in_the_background(monkeypatch):
     shm.wait_populated()
     shm.close()
     shm.unlink()
+
+
+def test_shared_dict_update_walks_attributes_and_is_all_or_nothing():
+    """SharedDict.update: a path may pass through a plain object (the DCP
+    metadata's ``storage_data`` dict is an attribute), a failing path leaves
+    everything untouched, and an empty served dict refuses patches."""
+    class Box(object):
+        def __init__(self):
+            self.storage_data = {"a": 1, "b": 2}
+
+    server = SharedDict(name="fcp_attr_%d" % os.getpid(), create=True)
+    client = SharedDict(name="fcp_attr_%d" % os.getpid(), create=False)
+    try:
+        assert client.update([(("x",), 1)]) is False  # nothing served yet
+        server._dict = {"meta": Box(), "lst": [10, 20], "cfg": {"step": 1}}
+        assert client.update([(("meta", "storage_data", "b"), 22), (("lst", 1), 21),
+                              (("cfg", "step"), 2), (("new_key",), "n")]) is True
+        d = server._dict
+        assert d["meta"].storage_data == {"a": 1, "b": 22} and d["lst"] == [10, 21]
+        assert d["cfg"] == {"step": 2} and d["new_key"] == "n"
+        # one bad path (list index out of range) -> nothing of the batch is applied
+        assert client.update([(("cfg", "step"), 3), (("lst", 5), 0)]) is False
+        assert d["cfg"] == {"step": 2}
+        # the last container must be a dict or a list: objects are not assigned into
+        assert client.update([(("meta", "storage_data"), {})]) is False
+        assert d["meta"].storage_data == {"a": 1, "b": 22}
+    finally:
+        client.unlink()
+        server.unlink()
