@@ -480,12 +480,12 @@ class SharedMemoryHandler(object):
     def no_checkpint_state(self):
         """True if no shard has ever been saved (handlers attach lazily, so
         this asks the meta dict, not the segment; SAVER:313-323)."""
-        meta_dict = self.metadata.get()
+        meta_dict = self.metadata.get_keys([DLROVER_CKPT_CONFIG_KEY])
         config = meta_dict.get(DLROVER_CKPT_CONFIG_KEY, None)
         return config is None or config.step == 0
 
     def get_checkpoint_config(self, default_config):
-        meta_dict = self.metadata.get()
+        meta_dict = self.metadata.get_keys([DLROVER_CKPT_CONFIG_KEY])
         return meta_dict.get(DLROVER_CKPT_CONFIG_KEY, default_config)
 
 

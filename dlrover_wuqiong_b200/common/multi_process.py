@@ -322,6 +322,8 @@ class SharedDict(LocalSocketComm):
             return DictMessage(meta_dict=self.get(**request.args))
         if request.method == "update":
             return DictMessage(meta_dict=_APPLIED if self._apply(**request.args) else None)
+        if request.method == "get_keys":
+            return DictMessage(meta_dict=self.get_keys(**request.args))
         raise ValueError("unknown method %s" % request.method)
 
     def _apply(self, updates):
@@ -386,6 +388,23 @@ class SharedDict(LocalSocketComm):
         if response.status == SUCCESS_CODE:
             self._dict = response.meta_dict
         return self._dict
+
+    def get_keys(self, keys):
+        """Only the given top-level keys (absent ones are left out).  The meta
+        tree of a few thousand tensors costs tens of ms to pickle; a reader
+        that wants the config alone need not pay for it.  A server that does
+        not know the request is asked for the whole dict instead.  The local
+        copy is not replaced."""
+        if self._server:
+            while not self._shared_queue.empty():
+                time.sleep(0.1)
+            return {k: self._dict[k] for k in keys if k in self._dict}
+        response = self._request(SocketRequest("get_keys", {"keys": list(keys)}))
+        if response.status == SUCCESS_CODE and isinstance(
+                getattr(response, "meta_dict", None), dict):
+            return response.meta_dict
+        whole = self.get()
+        return {k: whole[k] for k in keys if k in whole}
 
     def unlink(self):
         super().unlink()

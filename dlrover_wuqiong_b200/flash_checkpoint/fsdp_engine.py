@@ -293,6 +293,8 @@ class SharedMemoryReader(StorageReader):
         self.no_shard_data: Dict[str, Any] = {}
         self._checksums = None
         self._verified = False
+        self._meta_cache = None
+        self._meta_cache_step = None
 
     def reset(self, checkpoint_id: Union[str, os.PathLike, None] = None) -> None:
         pass
@@ -302,7 +304,15 @@ class SharedMemoryReader(StorageReader):
         return True
 
     def read_metadata(self) -> Metadata:
-        cached = self.shm_handler.metadata.get()
+        # one load reads the metadata twice (model, then optimizer): fetch the
+        # agent's copy once per FsdpCheckpointEngine.load()
+        conf = self.shm_handler.metadata.get_keys([DLROVER_CKPT_CONFIG_KEY]).get(
+            DLROVER_CKPT_CONFIG_KEY)
+        step = getattr(conf, "step", None)
+        cached = self._meta_cache
+        if cached is None or self._meta_cache_step != step:
+            cached = self._meta_cache = self.shm_handler.metadata.get()
+            self._meta_cache_step = step
         self.no_shard_data = cached["no_shard_data"]
         self._checksums = cached.get(FCP_CHECKSUM_KEY)
         return cached["dcp_metadata"]
@@ -746,6 +756,7 @@ class FsdpCheckpointEngine(CheckpointEngine):
         if passed and not self._shm_handler.no_checkpint_state():
             logger.info("Create a shared memory reader with step %s.", config.step)
             self._shm_reader._verified = False
+            self._shm_reader._meta_cache = None
             return self._shm_reader
         if not resume_path:
             resume_path = self._get_track_resume_path()

@@ -482,3 +482,27 @@ def test_shared_dict_update_walks_attributes_and_is_all_or_nothing():
     finally:
         client.unlink()
         server.unlink()
+
+
+def test_shared_dict_get_keys_fetches_a_subset_without_replacing_the_local_copy():
+    server = SharedDict(name="fcp_keys_%d" % os.getpid(), create=True)
+    client = SharedDict(name="fcp_keys_%d" % os.getpid(), create=False)
+    try:
+        client.set({"cfg": {"step": 5}, "big": list(range(1000)), "x": 1})
+        local_before = client.get(local=True)
+        assert client.get_keys(["cfg", "missing"]) == {"cfg": {"step": 5}}
+        assert server.get_keys(["x"]) == {"x": 1}
+        assert client.get(local=True) is local_before
+        # a server that does not know the request: the whole dict is fetched instead
+        real = server._handle
+
+        def old_server(request):
+            if request.method == "get_keys":
+                raise ValueError("unknown method")
+            return real(request)
+
+        server._handle = old_server
+        assert client.get_keys(["cfg"]) == {"cfg": {"step": 5}}
+    finally:
+        client.unlink()
+        server.unlink()
