@@ -12,11 +12,13 @@ the Trainer chose.  JSON side files (config, trainer_state) are written by the
 Trainer as usual.  ``transformers`` / ``deepspeed`` are imported lazily.
 """
 import os
+import re
 import shutil
 from typing import Optional
 
 import torch.distributed as dist
 
+from ..common.constants import CheckpointConstant
 from ..common.log import default_logger as logger
 from ..common.storage import PosixDiskStorage
 from ._hijack import redirected
@@ -103,6 +105,41 @@ def _build_trainer_class():
                 logger.info("Skip saving the checkpoint of step %s because the latest "
                             "checkpoint is not finished.", step)
                 shutil.rmtree(output_dir, ignore_errors=True)
+
+        # -- the newest folders may still be waiting for the agent: only what
+        # the tracker file vouches for is complete (hf_trainer.py:313-383)
+        def _get_last_checkpoint_step(self):
+            tracker = os.path.join(self.args.output_dir, CheckpointConstant.TRACER_FILE_NAME)
+            try:
+                with open(tracker) as f:
+                    return int(f.read().strip() or 0)
+            except (OSError, ValueError):
+                return 0
+
+        def get_last_checkpoint(self):
+            """Folder of the last *complete* checkpoint, False if there is none."""
+            step = self._get_last_checkpoint_step()
+            if step == 0:
+                return False
+            return os.path.join(self.args.output_dir, "%s-%s" % (PREFIX_CHECKPOINT_DIR, step))
+
+        def _rotate_checkpoints(self, use_mtime=False, output_dir=None):
+            limit = self.args.save_total_limit
+            if limit is None or limit <= 0:
+                return
+            last_step = self._get_last_checkpoint_step()
+            complete = []
+            for folder in self._sorted_checkpoints(use_mtime=use_mtime, output_dir=output_dir):
+                m = re.match(r".*%s-([0-9]+)$" % PREFIX_CHECKPOINT_DIR, str(folder))
+                if m and int(m.group(1)) <= last_step:
+                    complete.append(folder)
+            best = getattr(self.state, "best_model_checkpoint", None)
+            if best is not None and limit == 1 and complete and complete[-1] != best:
+                limit = 2  # never delete the checkpoint a resume would need
+            for folder in complete[:max(0, len(complete) - limit)]:
+                logger.info("Deleting older checkpoint [%s] due to save_total_limit = %s.",
+                            folder, self.args.save_total_limit)
+                shutil.rmtree(folder, ignore_errors=True)
 
     return FlashCkptTrainer
 

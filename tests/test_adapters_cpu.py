@@ -291,3 +291,91 @@ def test_hf_ddp_checkpointer_persists_every_captured_file(saver_env):
         opt_back = torch.load(os.path.join(out, "optimizer.pt"), weights_only=False)
         assert torch.equal(opt_back["state"][0]["exp_avg"], optimizer.state_dict()["state"][0]["exp_avg"])
         flash.async_save_engine.close()
+
+
+def test_flash_ckpt_trainer_on_a_stand_in_trainer(saver_env, monkeypatch):
+    """FlashCkptTrainer wraps whatever Trainer is installed.  The real one
+    cannot be built here (needs `accelerate`), so a stand-in `transformers`
+    with the four members the wrapper touches plays its part: a
+    `_save_checkpoint` that torch.saves weights / optimizer / scheduler / rng
+    the way HF does, `_get_output_dir`, `_sorted_checkpoints`, args + state.
+    hf_trainer_test.py:40-93 checks the same things on the real class."""
+    import sys
+    import types
+
+    import dlrover_wuqiong_b200.flash_checkpoint.hf_trainer as hf
+
+    class Trainer(object):
+        def __init__(self, model, args):
+            self.model, self.model_wrapped, self.args = model, model, args
+            self.optimizer = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
+            self.state = types.SimpleNamespace(global_step=0, best_model_checkpoint=None)
+            self.is_deepspeed_enabled = self.is_fsdp_enabled = False
+
+        def _get_output_dir(self, trial=None):
+            return self.args.output_dir
+
+        def _save_checkpoint(self, model, trial):
+            out = os.path.join(self.args.output_dir, "checkpoint-%d" % self.state.global_step)
+            os.makedirs(out, exist_ok=True)
+            assert self.args.save_safetensors is False  # the wrapper forces torch.save
+            torch.save(model.state_dict(), os.path.join(out, "pytorch_model.bin"))
+            torch.save(self.optimizer.state_dict(), os.path.join(out, "optimizer.pt"))
+            torch.save({"last_epoch": 3}, os.path.join(out, "scheduler.pt"))
+            torch.save({"cpu": torch.get_rng_state()}, os.path.join(out, "rng_state.pth"))
+            with open(os.path.join(out, "trainer_state.json"), "w") as f:
+                f.write("{}")
+
+        def _sorted_checkpoints(self, use_mtime=False, output_dir=None):
+            names = [d for d in os.listdir(output_dir) if d.startswith("checkpoint-")]
+            return [os.path.join(output_dir, d)
+                    for d in sorted(names, key=lambda d: int(d.split("-")[1]))]
+
+    fake = types.ModuleType("transformers")
+    fake.Trainer = Trainer
+    utils = types.ModuleType("transformers.trainer_utils")
+    utils.PREFIX_CHECKPOINT_DIR = "checkpoint"
+    fake.trainer_utils = utils
+    monkeypatch.setitem(sys.modules, "transformers", fake)
+    monkeypatch.setitem(sys.modules, "transformers.trainer_utils", utils)
+    monkeypatch.setattr(hf, "_TRAINER_CLS", None)
+    FlashCkptTrainer = hf.FlashCkptTrainer
+    assert issubclass(FlashCkptTrainer, Trainer)
+
+    with tempfile.TemporaryDirectory() as tmpdir:
+        args = types.SimpleNamespace(output_dir=tmpdir, save_safetensors=True, save_total_limit=2)
+        model = SimpleNet()
+        trainer = FlashCkptTrainer(model, args)
+        model.fc2(model.fc1(torch.randn(2, 64))).sum().backward()
+        trainer.optimizer.step()
+        # rotation: only folders the tracker vouches for are candidates
+        for step in (10, 20, 30, 40):
+            os.makedirs(os.path.join(tmpdir, "checkpoint-%d" % step))
+        assert trainer._get_last_checkpoint_step() == 0 and trainer.get_last_checkpoint() is False
+        with open(os.path.join(tmpdir, "dlrover_latest.txt"), "w") as f:
+            f.write("30")
+        assert trainer._get_last_checkpoint_step() == 30
+        assert trainer.get_last_checkpoint() == os.path.join(tmpdir, "checkpoint-30")
+        trainer._rotate_checkpoints(use_mtime=False, output_dir=tmpdir)
+        left = sorted(d for d in os.listdir(tmpdir) if d.startswith("checkpoint-"))
+        assert left == ["checkpoint-20", "checkpoint-30", "checkpoint-40"]  # 40 is not complete yet
+        # a save: every torch.save of the Trainer is captured, goes to shm and is
+        # persisted by the agent at the paths the Trainer chose
+        trainer.state.global_step = 50
+        trainer._save_checkpoint(model, None)
+        assert args.save_safetensors is True  # restored
+        agent = trainer.flash_checkpointer.ckpt_agent
+        names = {"pytorch_model.bin", "optimizer.pt", "scheduler.pt", "rng_state.pth"}
+        assert set(agent.paths) == names and names <= set(agent.state_dict)
+        out = os.path.join(tmpdir, "checkpoint-50")
+        tracker = os.path.join(tmpdir, "dlrover_latest.txt")
+        assert _wait_for(lambda: open(tracker).read() == "50")
+        assert _wait_for(lambda: all(os.path.exists(os.path.join(out, n)) for n in names))
+        weights = torch.load(os.path.join(out, "pytorch_model.bin"), weights_only=False)
+        assert torch.equal(weights["fc1.weight"], model.fc1.weight)
+        optim = torch.load(os.path.join(out, "optimizer.pt"), weights_only=False)
+        assert torch.equal(optim["state"][0]["momentum_buffer"],
+                           trainer.optimizer.state_dict()["state"][0]["momentum_buffer"])
+        assert os.path.exists(os.path.join(out, "trainer_state.json"))  # written by the Trainer itself
+        assert trainer.get_last_checkpoint() == out
+        trainer.flash_checkpointer.async_save_engine.close()
