@@ -133,6 +133,24 @@ def _host_copy_leaves(leaves, buffer):
         view.copy_(lf.tensor)
 
 
+def _write_shared_memory(value, meta, buffer):
+    """One host tensor -> its slot in `buffer` (SAVER:197-206); kept under the
+    reference's name for code written against that module."""
+    if value.numel():
+        _host_copy_leaves([_plan.Leaf(value, meta)], buffer)
+
+
+def _traverse_copy_to_shm(value, meta, buffer):
+    """Copy the tensors of `value` into `buffer` at the offsets of the meta
+    tree `meta` and refresh its non-tensor leaves (SAVER:174-194).  Host path
+    only; the handler itself pairs leaves once (plan.collect_leaves) and moves
+    CUDA tensors through the pack kernel."""
+    leaves = _plan.collect_leaves(value, meta)
+    if leaves is None:
+        raise KeyError("the state dict no longer has the structure of its meta tree")
+    _host_copy_leaves(leaves, buffer)
+
+
 class PendingSave(object):
     """Handle of a save whose bytes may still be in flight."""
 

@@ -16,7 +16,12 @@ from ..ckpt_saver import DeepSpeedCheckpointSaver
 from ..common import env_utils
 from ..common.constants import CheckpointConstant
 from ..common.storage import CheckpointStorage, get_checkpoint_storage
-from ._hijack import _read_file, redirected, torch_native_save
+from ._hijack import (  # noqa: F401  (torch_native_* re-exported, as the reference does)
+    _read_file,
+    redirected,
+    torch_native_load,
+    torch_native_save,
+)
 from .checkpointer import Checkpointer, StorageType
 from .deepspeed_engine import DeepSpeedCheckpointEngine
 

@@ -21,7 +21,7 @@ import torch.distributed as dist
 from ..common.constants import CheckpointConstant
 from ..common.log import default_logger as logger
 from ..common.storage import PosixDiskStorage
-from ._hijack import redirected
+from ._hijack import redirected, torch_native_load, torch_native_save  # noqa: F401
 from .deepspeed import AsyncCheckpointAgent
 from .deepspeed_engine import DeepSpeedCheckpointEngine
 from .engine import CheckpointEngine

@@ -506,3 +506,26 @@ def test_shared_dict_get_keys_fetches_a_subset_without_replacing_the_local_copy(
     finally:
         client.unlink()
         server.unlink()
+
+
+def test_reference_named_copy_helpers():
+    """_traverse_copy_to_shm / _write_shared_memory (SAVER:174-206) under the
+    reference's names: same bytes as the oracle's layout, scalars refreshed."""
+    from dlrover_wuqiong_b200 import plan
+    from dlrover_wuqiong_b200.ckpt_saver import _traverse_copy_to_shm, _write_shared_memory
+    from oracle import oracle
+    g = torch.Generator().manual_seed(4)
+    sd = {"a": {"w": torch.randn(5, 3, generator=g), "n": 1}, "l": [torch.arange(7), "x"],
+          "e": torch.empty(0)}
+    meta, leaves, total = plan.build_layout(sd)
+    buf = bytearray(total)
+    sd["a"]["n"] = 2
+    _traverse_copy_to_shm(sd, meta, buf)
+    _, _, expect = oracle.pack(sd)
+    assert bytes(buf) == expect.tobytes() and meta["a"]["n"] == 2
+    buf2 = bytearray(total)
+    for lf in leaves:
+        _write_shared_memory(lf.tensor, lf.meta, buf2)
+    assert buf2 == buf
+    with pytest.raises(KeyError):
+        _traverse_copy_to_shm({"a": {"w": sd["a"]["w"], "extra": torch.ones(1)}}, meta, buf)
