@@ -36,6 +36,7 @@ SYMBOLS = [
     ("fcp_plan_num_regions", _u64, [_vp]),
     ("fcp_host_register", _i, [_vp, _u64, ctypes.POINTER(_vp)]),
     ("fcp_host_unregister", _i, [_vp]),
+    ("fcp_host_chunk_crc32c", _i, [_vp, _u64, _u32, _vp, _i]),
     ("fcp_enable_peer", _i, [_i, _i]),
     ("fcp_ipc_export", _i, [_vp, _vp, _vp]),
     ("fcp_ipc_open", _i, [_vp, ctypes.POINTER(_vp)]),
@@ -265,6 +266,24 @@ def host_unregister(addr):
 def chunk_xxh64(packed_ptr, total_bytes, out_ptr, chunk_bytes=DEFAULT_CHUNK_BYTES, stream=0):
     """XXH64 of every chunk of a device-resident image into device memory."""
     check(lib().fcp_chunk_xxh64(packed_ptr, total_bytes, chunk_bytes, out_ptr, stream))
+
+
+def host_chunk_crc32c(buf, total_bytes=None, chunk_bytes=DEFAULT_CHUNK_BYTES, threads=0):
+    """Standard CRC-32C of every chunk of a packed image in host memory (a
+    buffer object or an address); host code only, no CUDA."""
+    if isinstance(buf, int):
+        addr = buf
+    else:
+        view = np.frombuffer(buf, dtype=np.uint8)
+        addr = view.ctypes.data
+        if total_bytes is None:
+            total_bytes = view.size
+    n = (total_bytes + chunk_bytes - 1) // chunk_bytes
+    out = np.zeros(n, dtype=np.uint32)
+    rc = lib().fcp_host_chunk_crc32c(addr, total_bytes, chunk_bytes, out.ctypes.data, threads)
+    if rc:
+        raise FcpError(rc, "fcp_host_chunk_crc32c failed")
+    return out
 
 
 def finish_checksums(raw, total_bytes, chunk_bytes=DEFAULT_CHUNK_BYTES):

@@ -154,11 +154,12 @@ def _traverse_copy_to_shm(value, meta, buffer):
 class PendingSave(object):
     """Handle of a save whose bytes may still be in flight."""
 
-    def __init__(self, handler, meta_dict, conf, engine):
+    def __init__(self, handler, meta_dict, conf, engine, host_leaves=None):
         self._handler = handler
         self._meta = meta_dict
         self._conf = conf
         self._engine = engine
+        self._host_leaves = host_leaves  # layout indices of host-resident leaves
         self._done = False
 
     def wait_packed(self):
@@ -178,7 +179,8 @@ class PendingSave(object):
             if sums is not None:
                 from .transfer import checksums_to_meta
                 self._meta[FCP_CHECKSUM_KEY] = checksums_to_meta(
-                    sums, self._engine.chunk_bytes, self._engine.stats.get("xxh64"))
+                    sums, self._engine.chunk_bytes, self._engine.stats.get("xxh64"),
+                    host_leaves=self._host_leaves)
             else:
                 self._meta.pop(FCP_CHECKSUM_KEY, None)
         else:
@@ -235,6 +237,13 @@ class SharedMemoryHandler(object):
 
     def reset(self):
         self._need_creation = True
+
+    def _wait_populated(self):
+        """Host writes into a segment this process just created wait for the
+        background threads that make it resident."""
+        wait = getattr(self.shared_memory, "wait_populated", None)
+        if wait is not None:
+            wait()
 
     def init_shared_memory(self, create=False, size=0):
         self._drop_engine()
@@ -325,20 +334,22 @@ class SharedMemoryHandler(object):
             meta_dict[DLROVER_CKPT_CONFIG_KEY] = conf
         conf.writing_shm = True
         engine = self._engine_for(leaves)
+        # writing_shm=True reaches the agent before the first byte of the
+        # image changes (SAVER:283-288): a trainer that dies mid-save then
+        # leaves a meta that says so, and neither the agent nor a restarted
+        # trainer's plain load_state_dict() (CPU views, no CRC) trusts the
+        # image.  With the agent holding this layout the message is the config
+        # alone (a path-wise update, ~0.2 ms).
+        self._announce(meta_dict, conf)
         if engine is not None and self.shared_memory is not None:
-            # GPU path: get the pack kernels going first, publish the
-            # "being rewritten" meta while they run.  The caller holds the shm
-            # lock for the whole save, so the agent cannot read in between;
-            # a trainer that dies in the ~2 ms window leaves the lock held
-            # (agent skips the shard) and a torn image fails its CRC.
             engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf,
                               ready=getattr(self.shared_memory, "wait_populated", None))
-            self._announce(meta_dict, conf)
-            return PendingSave(self, meta_dict, conf, engine)
-        self._announce(meta_dict, conf)
+            host_leaves = [i for i, lf in enumerate(leaves) if not lf.is_cuda]
+            return PendingSave(self, meta_dict, conf, engine, host_leaves)
         if self.shared_memory is None:
             # nothing but empty tensors / scalars: the meta carries it all
             return PendingSave(self, meta_dict, conf, None)
+        self._wait_populated()
         _host_copy_leaves(leaves, self.shared_memory.buf)
         return PendingSave(self, meta_dict, conf, None)
 
@@ -354,9 +365,11 @@ class SharedMemoryHandler(object):
 
         ``into``: a state dict of the same structure whose tensors receive the
         bytes in place (CUDA tensors through the scatter kernel).  ``device``:
-        allocate fresh tensors there instead.  Both verify the CRC-32C
-        recorded at save time.  Returns {} when the shm holds no complete
-        checkpoint."""
+        allocate fresh tensors there instead (leaves that were host-resident
+        at save time stay on the host).  Given both, `into` may cover only
+        part of the structure (say, the optimizer shards) and the rest is
+        allocated on `device`.  All variants verify the CRC-32C recorded at
+        save time.  Returns {} when the shm holds no complete checkpoint."""
         meta_dict = self.metadata.get()
         config = meta_dict.get(DLROVER_CKPT_CONFIG_KEY, CheckpointConfig())
         if not meta_dict or config.writing_shm:
@@ -380,25 +393,27 @@ class SharedMemoryHandler(object):
             self.init_shared_memory(create=False)
         sums = meta_dict.get(FCP_CHECKSUM_KEY)
         buf = self.shared_memory.buf if self.shared_memory else b""
-        return {name: raw_ckpt.RawImage(sub, buf, config.step, sums)
+        return {name: raw_ckpt.RawImage(sub, buf, config.step, sums, total=len(buf))
                 for name, sub in _strip_private(meta_dict).items()
                 if name != DLROVER_CKPT_CONFIG_KEY}
 
     def _load_into(self, meta_dict, into, device):
         total = self.shared_memory.size
         public = _strip_private(meta_dict)
-        if into is None:
-            dev = torch.device(device)
+        dev = torch.device(device) if device is not None else None
+        # leaves that lived in host memory when the image was packed (rng
+        # states, a CPU `step`) come back as host tensors: their consumers
+        # (torch.set_rng_state ...) want them there
+        host_idx = set((meta_dict.get(FCP_CHECKSUM_KEY) or {}).get("host_leaves") or ())
 
-            def alloc(m):
-                if isinstance(m, TensorMeta):
-                    return torch.empty(m.shape, dtype=m.dtype, device=dev)
-                return m
+        def alloc(index, m):
+            if dev is None:
+                raise ValueError("`into` does not match the structure of the checkpoint "
+                                 "in memory (pass device= to allocate what it lacks)")
+            where = "cpu" if index in host_idx else dev
+            return torch.empty(m.shape, dtype=m.dtype, device=where)
 
-            into = _traverse_state_dict(public, alloc)
-        leaves = _plan.collect_leaves(into, public, refresh=False)
-        if leaves is None or len(leaves) != _plan.count_tensor_metas(public):
-            raise ValueError("`into` does not match the structure of the checkpoint in memory")
+        leaves = _plan.pair_or_alloc(public, into, alloc)
         engine = self._engine_for(leaves)
         if engine is not None:
             from .transfer import checksums_from_meta
@@ -463,9 +478,14 @@ class SharedMemoryHandler(object):
         engine = self._engine_for(leaves)
         if engine is not None and mm is not None:
             from .transfer import checksums_from_meta
+            # sums of the payload's own windows (files written before they
+            # existed carry the whole image's sums, usable only when the
+            # payload IS the whole image)
+            expected = checksums_from_meta(header.get("payload_checksums"), total,
+                                           engine.chunk_bytes)
             image = header.get("image") or {}
-            expected = None
-            if image.get("offset") == 0:  # windows line up with the payload
+            if expected is None and image.get("offset") == 0 \
+                    and image.get("total", total) == total:
                 expected = checksums_from_meta(image.get("checksums"), total, engine.chunk_bytes)
             engine.restore(leaves, total, mm, expected, transient=True)
             self.last_stats = dict(engine.stats)
@@ -482,6 +502,42 @@ class SharedMemoryHandler(object):
             return next(it).tensor if isinstance(m, TensorMeta) else m
 
         return _traverse_state_dict(meta, fill)
+
+    def verify_image(self):
+        """Recompute the CRC-32C of every chunk of the shm image on the host
+        and compare with the sums the pack kernel recorded in the meta
+        (FCP_CHECKSUM_KEY).  The agent calls this before it persists a shard:
+        whatever the lock state was, an image that was torn by a trainer dying
+        mid-save, or that does not belong to the meta next to it, never
+        reaches storage.  No-op for images without recorded sums (host-only
+        state dicts).  Host code only (libfcp.so's SSE4.2 routine, no CUDA).
+        Returns the number of chunks checked."""
+        meta_dict = self.metadata.get()
+        entry = meta_dict.get(FCP_CHECKSUM_KEY) if meta_dict else None
+        if not entry or entry.get("algo") != "crc32c":
+            return 0
+        if self.shared_memory is None or self._need_creation or self._segment_replaced():
+            self.init_shared_memory(create=False)
+        if not self.shared_memory:
+            return 0
+        from . import _native
+        chunk = int(entry["chunk_bytes"])
+        expected = entry["sums"]
+        total = self.shared_memory.size
+        t0 = time.time()
+        got = _native.host_chunk_crc32c(self.shared_memory.buf, total, chunk)
+        if len(got) != len(expected):
+            raise _native.ChecksumMismatch(
+                -74, "the shm image has %d chunks, its meta records %d"
+                % (len(got), len(expected)))
+        for i, (a, b) in enumerate(zip(got.tolist(), expected)):
+            if a != int(b):
+                raise _native.ChecksumMismatch(
+                    -74, "shm image is corrupt: CRC-32C of chunk %d is %08x, recorded %08x"
+                    % (i, a, int(b)))
+        logger.info("verified %d chunk checksums of the shm image (%.2f GB) in %.2fs",
+                    len(got), total / 1e9, time.time() - t0)
+        return len(got)
 
     def _segment_replaced(self):
         """The writer re-creates the segment when the layout changes; a reader
@@ -786,6 +842,8 @@ class AsyncCheckpointSaver(metaclass=ABCMeta):
         over the shm (SAVER:914-921), or with DLROVER_FCP_PERSIST_FORMAT=raw
         the image bytes themselves (raw_ckpt.py)."""
         handler = self._shm_handlers[local_shard_id]
+        if os.getenv("FCP_AGENT_VERIFY", "1") == "1":
+            handler.verify_image()  # raises ChecksumMismatch: a torn image is never persisted
         if raw_ckpt.persist_format() == "raw":
             states, write_func = handler.load_raw_images(), raw_ckpt.write_raw
         else:
@@ -998,6 +1056,8 @@ class FsdpDcpSaver(CommonDirCheckpointSaver):
             # a mapping made before that still shows the old image
             handler.init_shared_memory(create=False)
         assert handler.shared_memory is not None
+        if os.getenv("FCP_AGENT_VERIFY", "1") == "1":
+            handler.verify_image()
         self.storage.write(handler.shared_memory.buf, path)
         if self._is_agent_rank_0 and local_shard_id == 0:
             meta_dict = handler.metadata.get()

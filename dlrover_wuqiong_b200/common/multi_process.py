@@ -433,6 +433,7 @@ class _Populator(object):
         self._done = [False] * self._blocks
         self._front = 0  # every block below this index is resident
         self._cv = threading.Condition()
+        self._give_up = False
         self._libc = ctypes.CDLL(None, use_errno=True)
         self._libc.madvise.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
         self._threads = [threading.Thread(target=self._work, daemon=True, name="shm-populate-%d" % i)
@@ -449,10 +450,12 @@ class _Populator(object):
                 self._next += 1
             lo = i * _POPULATE_BLOCK
             n = min(_POPULATE_BLOCK, self._size - lo)
-            if self._libc.madvise(self._addr + lo, n, _MADV_POPULATE_WRITE) != 0:
-                # older kernel: touch the pages instead (the segment was just
-                # created, so it holds zeros anyway)
-                ctypes.memset(self._addr + lo, 0, n)
+            if not self._give_up and \
+                    self._libc.madvise(self._addr + lo, n, _MADV_POPULATE_WRITE) != 0:
+                # kernel without MADV_POPULATE_WRITE (< 5.14): leave the pages
+                # to fault in on first use.  Nothing may be WRITTEN here: the
+                # owner is free to fill the segment while these threads run.
+                self._give_up = True
             with self._cv:
                 self._done[i] = True
                 while self._front < self._blocks and self._done[self._front]:

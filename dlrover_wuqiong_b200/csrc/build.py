@@ -7,7 +7,7 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SOURCES = ["fcp.cu"]
+SOURCES = ["fcp.cu", "fcp_host.cpp"]
 HEADERS = ["fcp_crc.h", "fcp_kernels.cuh", "fcp_kernels2.cuh",
            os.path.join("..", "..", "include", "fcp.h")]
 TARGET = os.path.join(HERE, "libfcp.so")

@@ -188,6 +188,10 @@ struct fcp_plan {
   uint64_t copy_piece = 0;  // split host copies at multiples of this (0 = never)
   uint32_t kernel_flags = 0;
   std::vector<fcp_desc> h_descs;
+  fcp_desc* h_pinned = nullptr;  // pinned mirror of h_descs: source of the uploads
+  bool descs_dirty = false;      // h_pinned is newer than d_descs
+  bool upload_pending = false;   // ev_upload has been recorded
+  cudaEvent_t ev_upload = nullptr;
   fcp_desc* d_descs = nullptr;
   uint32_t* d_region_sums = nullptr;
   uint32_t* d_work = nullptr;  // run-distribution counters of the kernels (Args.work)
@@ -209,10 +213,18 @@ struct fcp_plan {
 
 namespace {
 
-int plan_upload(fcp_plan* p) {
-  if (p->n_desc == 0) return 0;
-  FCP_CUDA(cudaMemcpy(p->d_descs, p->h_descs.data(),
-                      sizeof(fcp_desc) * p->n_desc, cudaMemcpyHostToDevice));
+// Bring the device copy of the descriptor table up to date ON THE STREAM the
+// kernels are about to be launched on (from pinned memory, so the copy is an
+// ordinary stream operation): ordered before those kernels whatever kind of
+// stream it is.  A synchronous pageable cudaMemcpy would only be ordered
+// against the legacy default stream and blocking streams.
+int plan_sync_descs(fcp_plan* p, cudaStream_t st) {
+  if (!p->descs_dirty || p->n_desc == 0) return 0;
+  FCP_CUDA(cudaMemcpyAsync(p->d_descs, p->h_pinned, sizeof(fcp_desc) * p->n_desc,
+                           cudaMemcpyHostToDevice, st));
+  FCP_CUDA(cudaEventRecord(p->ev_upload, st));
+  p->upload_pending = true;
+  p->descs_dirty = false;
   return 0;
 }
 
@@ -379,6 +391,8 @@ int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
       return bail(fail(-ENOMEM, "%s failed: %s", #expr, cudaGetErrorString(e_))); \
   } while (0)
   FCP_TRY(cudaMalloc(&p->d_descs, sizeof(fcp_desc) * (n ? n : 1)));
+  FCP_TRY(cudaMallocHost(&p->h_pinned, sizeof(fcp_desc) * (n ? n : 1)));
+  FCP_TRY(cudaEventCreateWithFlags(&p->ev_upload, cudaEventDisableTiming));
   FCP_TRY(cudaMalloc(&p->d_region_sums,
                      sizeof(uint32_t) * (p->n_regions ? p->n_regions : 1)));
   FCP_TRY(cudaMalloc(&p->d_chunk_sums,
@@ -394,8 +408,14 @@ int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
   FCP_TRY(cudaEventCreate(&p->ev_kern_b));
   FCP_TRY(cudaEventCreate(&p->ev_kern_e));
 #undef FCP_TRY
-  rc = plan_upload(p);
-  if (rc) return bail(rc);
+  if (n) {
+    memcpy(p->h_pinned, descs, sizeof(fcp_desc) * n);
+    p->descs_dirty = true;
+    rc = plan_sync_descs(p, p->copy_stream);
+    if (rc) return bail(rc);
+    if (cudaStreamSynchronize(p->copy_stream) != cudaSuccess)
+      return bail(fail(-EIO, "descriptor upload failed"));
+  }
   *out = p;
   return 0;
 }
@@ -412,9 +432,14 @@ int fcp_plan_update_ptrs(fcp_plan* p, const void* const* ptrs, uint64_t n) {
       changed = true;
     }
   if (!changed) return 0;
-  DeviceGuard g(p->device);
-  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
-  return plan_upload(p);
+  // the pinned mirror may still be the source of an upload in flight
+  if (p->upload_pending) {
+    FCP_CUDA(cudaEventSynchronize(p->ev_upload));
+    p->upload_pending = false;
+  }
+  for (uint64_t i = 0; i < n; ++i) p->h_pinned[i].ptr = ptrs[i];
+  p->descs_dirty = true;  // uploaded by the next launch, on its stream
+  return 0;
 }
 
 void fcp_plan_destroy(fcp_plan* p) {
@@ -426,6 +451,8 @@ void fcp_plan_destroy(fcp_plan* p) {
   if (p->d_work) cudaFree(p->d_work);
   if (p->d_chunk_sums) cudaFree(p->d_chunk_sums);
   if (p->h_chunk_sums) cudaFreeHost(p->h_chunk_sums);
+  if (p->h_pinned) cudaFreeHost(p->h_pinned);
+  if (p->ev_upload) cudaEventDestroy(p->ev_upload);
   if (p->ring) cudaFreeHost(p->ring);
   if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   cudaEvent_t evs[] = {p->ev_begin, p->ev_packed, p->ev_done, p->ev_kern_b,
@@ -641,9 +668,11 @@ static int plan_kernels_only(fcp_plan* p, void* packed, int direction,
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = plan_sync_descs(p, st);
+  if (rc) return rc;
   FCP_CUDA(cudaEventRecord(p->ev_kern_b, st));
   p->last_launches = 0;
-  int rc = plan_launch(p, packed, direction, checksum, 0, p->n_chunks, st);
+  rc = plan_launch(p, packed, direction, checksum, 0, p->n_chunks, st);
   if (rc) return rc;
   FCP_CUDA(cudaEventRecord(p->ev_kern_e, st));
   p->last_has_sums = checksum != 0;
@@ -683,8 +712,9 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = plan_sync_descs(p, st);
+  if (rc) return rc;
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
-  int rc = 0;
   p->last_launches = 0;
   if (mode == FCP_MODE_DIRECT) {
     void* alias = nullptr;
@@ -804,7 +834,8 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc = 0;
+  int rc = plan_sync_descs(p, st);
+  if (rc) return rc;
   p->last_launches = 0;
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
   if (mode == FCP_MODE_DIRECT) {
@@ -861,10 +892,12 @@ int fcp_restore_from_device(fcp_plan* p, const void* packed, int checksum,
   DeviceGuard g(p->device);
   if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = plan_sync_descs(p, st);
+  if (rc) return rc;
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
   p->last_launches = 0;
-  int rc = plan_launch(p, const_cast<void*>(packed), 1, checksum, 0,
-                       p->n_chunks, st);
+  rc = plan_launch(p, const_cast<void*>(packed), 1, checksum, 0,
+                   p->n_chunks, st);
   if (rc) return rc;
   if (checksum && p->n_chunks)
     FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
@@ -912,6 +945,10 @@ int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
     p->ring_slot_bytes = slot;
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  {
+    int rc0 = plan_sync_descs(p, st);
+    if (rc0) return rc0;
+  }
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
   FCP_CUDA(cudaStreamSynchronize(st));  // staging is free, caller's work done
   const uint64_t n_slices = ceil_div(p->total, slot);

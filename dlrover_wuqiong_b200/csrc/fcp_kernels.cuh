@@ -81,6 +81,17 @@ __device__ __forceinline__ void prefetch_l2(uintptr_t p, uint32_t bytes) {
                : "memory");
 }
 
+// the same, cut off at `lim`: nothing at or beyond that address is requested
+// (the read side ends there — end of the tensor or of the packed image — and
+// what follows may not be mapped)
+__device__ __forceinline__ void prefetch_l2_upto(uintptr_t p, uint32_t bytes,
+                                                 uintptr_t lim) {
+  if (p >= lim) return;
+  const uint64_t room = (lim - p) & ~static_cast<uint64_t>(15);
+  const uint32_t n = room < bytes ? static_cast<uint32_t>(room) : bytes;
+  if (n) prefetch_l2(p, n);
+}
+
 // bytes [m, m+32) of the 64-byte concatenation lo||hi, 0 < m < 32
 __device__ __forceinline__ W8 extract32(const W8& lo, const W8& hi,
                                         uint32_t m) {

@@ -185,6 +185,10 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
       // request, so the 256-bit loads mostly hit L2 instead of waiting on HBM
       const uintptr_t rd0 = (PACK ? c.ptr + (rbase - c.off)
                                   : reinterpret_cast<uintptr_t>(a.packed + rbase)) & ~uintptr_t(15);
+      // where the read side ends: the prefetch of the last batch reaches a few
+      // bytes past the region and must not leave the tensor / the image
+      const uintptr_t rd_lim = PACK ? c.ptr + (c.end - c.off)
+                                    : reinterpret_cast<uintptr_t>(a.packed) + total;
       if (PACK && mis != 0) {
         // source not 32-byte aligned relative to the image: fetch the two
         // aligned words around each word (the second is the next lane's
@@ -193,7 +197,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
 #pragma unroll 1
         for (int row = 0; row < kRows; row += 2) {
           if (lane == 0 && pf && row + 2 < kRows)
-            prefetch_l2(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 64);
+            prefetch_l2_upto(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 64, rd_lim);
           W8 lo[2], hi[2];
 #pragma unroll
           for (int k = 0; k < 2; ++k) {
@@ -222,7 +226,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
 #pragma unroll 1
         for (int row = 0; row < kRows; row += 2) {
           if (lane == 0 && pf && row + 2 < kRows)
-            prefetch_l2(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 48);
+            prefetch_l2_upto(rd0 + (row + 2) * kRowBytes, 2 * kRowBytes + 48, rd_lim);
           W8 v[2], hi[2];
 #pragma unroll
           for (int k = 0; k < 2; ++k) {
@@ -254,7 +258,7 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
 #pragma unroll 1
         for (int row = 0; row < kRows; row += kBatch) {
           if (lane == 0 && pf && row + kBatch < kRows)
-            prefetch_l2(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16);
+            prefetch_l2_upto(rd0 + (row + kBatch) * kRowBytes, kBatch * kRowBytes + 16, rd_lim);
           W8 v[kBatch];
 #pragma unroll
           for (int k = 0; k < kBatch; ++k)

@@ -152,7 +152,11 @@ class DeepSpeedCheckpointer(Checkpointer):
                         load_module_only=False, custom_load_fn=None):
         """Same arguments as DeepSpeedEngine.load_checkpoint; state that is
         still in shared memory is served from there."""
-        self._ckpt_agent.state_dict = self._async_save_engine.load()
+        # GPU jobs: tensors arrive on the current CUDA device through the
+        # scatter kernel instead of as CPU views DeepSpeed would copy up one
+        # by one (deepspeed.py:240-256 in the reference)
+        self._ckpt_agent.state_dict = self._async_save_engine.load(
+            device=self._async_save_engine.restore_device())
         with redirected(load=self._ckpt_agent.load):
             return self.engine.load_checkpoint(
                 load_dir=load_dir, tag=tag, load_module_strict=load_module_strict,

@@ -291,6 +291,7 @@ class CheckpointEngine(metaclass=ABCMeta):
         the in-place GPU restore of SharedMemoryHandler.load_state_dict; a
         checksum mismatch counts as "nothing valid"."""
         self.wait_async_save()
+        self._memory_restore_wrecked_into = False
         self._restore_memory_from_replica()
         state_dict = {}
         config = self._shm_handler.get_checkpoint_config(CheckpointConfig())
@@ -305,10 +306,48 @@ class CheckpointEngine(metaclass=ABCMeta):
                 if not isinstance(e, ChecksumMismatch):
                     raise
                 logger.error("checkpoint in memory is corrupt (%s); falling back to storage", e)
+                # the scatter kernel verifies while it writes: the tensors of
+                # `into` now hold bytes of the corrupt image
+                self._memory_restore_wrecked_into = into is not None
                 return config.step, {}
             state_dict.pop(DLROVER_CKPT_CONFIG_KEY, None)
             logger.info("Load checkpoint at step %s from memory.", config.step)
         return config.step, state_dict
+
+    def restore_device(self):
+        """Where the framework adapters (Megatron, DeepSpeed) ask for restored
+        tensors.  The reference hands them CPU views of the shm and the
+        framework's ``load_state_dict`` then issues one pageable host->device
+        copy per tensor (megatron.py:92-108, megatron_dist_ckpt.py:685-686,
+        deepspeed_engine.py:148-158).  When the image in memory was written
+        from CUDA tensors (it carries chunk checksums) and this process has a
+        GPU, the adapters instead get fresh tensors on the current CUDA
+        device, filled by one verified scatter launch, and the framework's
+        copies become device-to-device.  None = reference behaviour (CPU
+        views).  FCP_RESTORE_DEVICE=cpu|cuda overrides the choice."""
+        choice = os.getenv("FCP_RESTORE_DEVICE", "auto").lower()
+        if choice == "cpu" or not torch.cuda.is_available():
+            return None
+        device = torch.device("cuda", torch.cuda.current_device())
+        if choice == "cuda":
+            return device
+        from ..ckpt_saver import FCP_CHECKSUM_KEY
+        try:
+            gpu_image = bool(self._shm_handler.metadata.get_keys([FCP_CHECKSUM_KEY]))
+        except Exception:  # noqa: BLE001 - no agent, nothing in memory
+            gpu_image = False
+        return device if gpu_image else None
+
+    def _raise_if_into_wrecked(self, restored):
+        """After the storage fallback: if the in-place restore from memory
+        failed its checksums (so `into` was partly overwritten) and storage had
+        nothing either, the caller's live tensors are garbage — say so instead
+        of returning an empty dict that reads as "no checkpoint, keep going"."""
+        if getattr(self, "_memory_restore_wrecked_into", False) and not restored:
+            raise RuntimeError(
+                "the checkpoint in shared memory failed its CRC-32C check while it was being "
+                "restored in place, and no checkpoint in storage could replace it: the tensors "
+                "passed as into= were partly overwritten and must be re-initialised")
 
     def _restore_memory_from_replica(self):
         """If this node lost its shm (it was replaced), fetch the shard from a
@@ -320,6 +359,7 @@ class CheckpointEngine(metaclass=ABCMeta):
         if byte_tensor is not None and meta and not self._shm_handler.shared_memory:
             shm_size = byte_tensor.size()[0]
             self._shm_handler.init_shared_memory(create=True, size=shm_size)
+            self._shm_handler._wait_populated()
             torch.frombuffer(self._shm_handler.shared_memory.buf,
                              dtype=torch.uint8).copy_(byte_tensor)
             self._shm_handler.metadata.set(meta)

@@ -132,6 +132,14 @@ def _item_leaf(data, offset):
     return Leaf(t, meta)
 
 
+def _wait_populated(shm):
+    """A segment this process just created is still being made resident by
+    background threads; host writes wait for them."""
+    wait = getattr(shm, "wait_populated", None)
+    if wait is not None:
+        wait()
+
+
 def _host_write_leaves(leaves, buf):
     """Host-only state (CPU FSDP in the reference's tests): plain copies."""
     for lf in leaves:
@@ -253,7 +261,9 @@ class SharedMemoryWriter(StorageWriter):
         h = self.shm_handler
         if h.shared_memory is None or h.shared_memory.size != offset:
             if h.shared_memory is not None:
+                h._drop_engine()  # unpin the old mapping before it is unmapped
                 h.shared_memory.close()
+                h.shared_memory = None
             if offset:
                 h.init_shared_memory(create=True, size=offset)
         self.checksums = None
@@ -268,6 +278,7 @@ class SharedMemoryWriter(StorageWriter):
                 else:
                     self.finish_transfer()
             else:
+                _wait_populated(h.shared_memory)
                 _host_write_leaves(leaves, h.shared_memory.buf)
         self.metadata["no_shard_data"] = no_shard_data
         fut: Future = Future()

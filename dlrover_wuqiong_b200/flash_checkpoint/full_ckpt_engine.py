@@ -95,7 +95,9 @@ class FullCheckpointEngine(CheckpointEngine):
         if into is not None:
             names = list(into.keys())
             into = into[names[0]] if len(names) == 1 else None
-        return self._load_from_storage(resume_path, into=into)
+        restored = self._load_from_storage(resume_path, into=into)
+        self._raise_if_into_wrecked(restored)
+        return restored
 
     def _load_from_storage(self, resume_path="", into=None):
         """`into`: the live state dict to fill in place (raw image files go

@@ -52,6 +52,7 @@ class MegatronCheckpointer(Singleton):
                  save_timeout=CheckpointConstant.SAVE_TIMEOUT, replica_count=0):
         self.state_dict = {}
         self.paths = {}
+        self._restored = {}  # state names of the last memory restore not yet handed out
         self.checkpoint_dir = checkpoint_dir
         self.storage = storage if storage else PosixDiskStorage()
         self.engine = MegatronCheckpointEngine(
@@ -69,17 +70,27 @@ class MegatronCheckpointer(Singleton):
                              "%s or %s." % (_MODEL_SD_NAME, _DIST_OPTIM_SD_NAME))
         self.state_dict[name] = state_dict
         self.paths[name] = path
+        self._restored = {}
 
     def load(self, path: str, **kwargs):
         """torch.load stand-in: shared memory first, then the file."""
         if not isinstance(path, str):
             return torch_native_load(path)
-        # engine.load returns (step, state_dict); the reference treats the
-        # tuple as the dict, so its memory restore never hits (megatron.py:98-108)
-        _, state_dict = self.engine.load(resume_path=path)
         name = _state_name(path)
+        # Megatron reads model_optim_rng.pt and then distrib_optim.pt: both
+        # names come out of ONE restore of the image
+        if name and name in self._restored:
+            return self._restored.pop(name)
+        # engine.load returns (step, state_dict); the reference treats the
+        # tuple as the dict, so its memory restore never hits (megatron.py:98-108).
+        # On a GPU job the tensors arrive on the current CUDA device through
+        # the scatter kernel (engine.restore_device), not as CPU views that
+        # Megatron would copy up one pageable transfer at a time.
+        _, state_dict = self.engine.load(resume_path=path,
+                                         device=self.engine.restore_device())
         if name and name in state_dict:
-            return state_dict[name]
+            self._restored = dict(state_dict)
+            return self._restored.pop(name)
         return self.storage.read_state_dict(path, lambda p: _read_file(p, "cpu"))
 
     def update_tracer_file(self, iteration: int):

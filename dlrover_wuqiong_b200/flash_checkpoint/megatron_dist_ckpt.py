@@ -113,12 +113,15 @@ def get_chained_optimizer_parameter_state(chained_optimizer):
 
 
 def load_parameter_state_from_state_dict(dist_optimizer, state_dict):
-    """Copy restored shards back into the live tensors (per-tensor path; the
-    engine's ``load(into=...)`` does the same in one scatter launch)."""
+    """Copy restored shards into the live tensors (megatron_dist_ckpt.py:657-698
+    in the reference).  On a GPU job `state_dict` already lives on the device
+    (see _load_checkpoint_from_memory), so these are device-to-device copies;
+    a shard restored in place (``engine.load(into=...)``) is skipped."""
     for bucket_idx, group_index, group_order, tensors in _param_state_slots(dist_optimizer):
         restored = state_dict[bucket_idx][group_index][group_order]
         for key, t in tensors.items():
-            t.data.copy_(restored[key])
+            if restored[key] is not t:
+                t.data.copy_(restored[key])
 
 
 def load_chained_optimizer_parameter_state(chained_optimizer, states):
@@ -195,7 +198,11 @@ def save_checkpoint(iteration, model, optimizer, opt_param_scheduler,
 
 
 def _load_checkpoint_from_memory(checkpointer, into=None):
-    step, state_dict = checkpointer.engine.load(into=into)
+    # GPU jobs: fresh tensors on the current CUDA device through one verified
+    # scatter launch; model.load_state_dict / load_parameter_state_from_state_dict
+    # below then copy device-to-device instead of one pageable H2D per tensor
+    step, state_dict = checkpointer.engine.load(
+        into=into, device=checkpointer.engine.restore_device())
     return (state_dict.get(CheckpointConstant.MODEL_STATES_NAME, {}),
             state_dict.get(CheckpointConstant.OPTIM_STATES_NAME, {}),
             "iter_{:07d}".format(step), False)

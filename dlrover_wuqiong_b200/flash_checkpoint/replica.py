@@ -133,6 +133,7 @@ class ShardCkptReplicaManager(CkptReplicaManger):
             if handler is None:
                 handler = SharedMemoryHandler(local_rank=config.rank)
                 handler.init_shared_memory(create=True, size=shm_tensor.numel())
+                handler._wait_populated()
                 self._rank_shms[config.rank] = handler
             local = torch.frombuffer(handler.shared_memory.buf, dtype=torch.uint8)
             local.copy_(shm_tensor[:local.numel()])

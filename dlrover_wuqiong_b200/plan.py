@@ -132,3 +132,45 @@ def count_tensor_metas(meta_tree):
 
     traverse_state_dict(meta_tree, visit)
     return n
+
+
+def pair_or_alloc(meta_tree, into, alloc):
+    """Leaves for a restore: walk `meta_tree`; where `into` (a possibly
+    partial mirror of the tree, or None) holds a tensor at the same place it
+    receives the bytes, elsewhere ``alloc(index, meta)`` supplies a fresh
+    tensor (`index` = position of the leaf in layout order).  A tensor in
+    `into` whose dtype or element count differs from the checkpoint's raises
+    ValueError.  Returns the leaf list in layout order."""
+    leaves = []
+    missing = object()
+
+    def child(container, key):
+        if container is missing or container is None:
+            return missing
+        if isinstance(container, Mapping):
+            return container.get(key, missing)
+        if isinstance(container, list):
+            return container[key] if isinstance(key, int) and key < len(container) else missing
+        return missing
+
+    def walk(m, v, path):
+        if isinstance(m, Mapping):
+            for k, x in m.items():
+                walk(x, child(v, k), path + (k,))
+        elif isinstance(m, list):
+            for i, x in enumerate(m):
+                walk(x, child(v, i), path + (i,))
+        elif isinstance(m, TensorMeta):
+            if torch.is_tensor(v):
+                if v.numel() != m.numel or v.dtype != m.dtype:
+                    raise ValueError(
+                        "`into` does not match the checkpoint at %s: %s%s there, %s%s here"
+                        % ("/".join(map(str, path)), m.dtype, tuple(m.shape), v.dtype,
+                           tuple(v.shape)))
+                t = v
+            else:
+                t = alloc(len(leaves), m)
+            leaves.append(Leaf(t, m))
+
+    walk(meta_tree, into if into is not None else missing, ())
+    return leaves

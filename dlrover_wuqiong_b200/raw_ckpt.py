@@ -83,11 +83,12 @@ class RawImage(object):
     """What the saver hands to ``storage.write_state_dict(..., write_raw)`` in
     place of a state dict: one state name's meta subtree plus the image."""
 
-    def __init__(self, meta_subtree, image_buf, step=0, checksums=None):
+    def __init__(self, meta_subtree, image_buf, step=0, checksums=None, total=None):
         self.meta = meta_subtree
         self.buf = image_buf
         self.step = step
         self.checksums = checksums  # the image's _FCP_CHECKSUMS meta entry
+        self.total = len(image_buf) if total is None else total  # bytes of the whole image
 
     def __bool__(self):
         return bool(self.meta)
@@ -103,6 +104,25 @@ def _pwrite_all(fd, view, offset):
         done += os.pwrite(fd, view[done:], offset + done)
 
 
+def _payload_checksums(raw_image, lo, hi):
+    """Checksum entry for payload bytes [lo, hi) of the image: the image's own
+    sums when the payload is the whole image, else computed here on the host
+    (only images that carry sums get any)."""
+    sums = raw_image.checksums
+    if not sums or sums.get("algo") != "crc32c" or hi <= lo:
+        return None
+    if lo == 0 and hi == raw_image.total:
+        return sums
+    from . import _native
+    chunk = int(sums["chunk_bytes"])
+    view = memoryview(raw_image.buf)[lo:hi]
+    try:
+        got = _native.host_chunk_crc32c(view, hi - lo, chunk)
+    finally:
+        view.release()
+    return {"algo": "crc32c", "chunk_bytes": chunk, "sums": got.tolist()}
+
+
 def write_raw(raw_image, path):
     """Write one state name's byte range and meta to `path` (the
     ``write_func`` of ``CheckpointStorage.write_state_dict``)."""
@@ -111,7 +131,11 @@ def write_raw(raw_image, path):
               "meta": _encode_meta(raw_image.meta, lo),
               # CRC-32C of the image's fixed windows; window k covers image
               # bytes [k*chunk, (k+1)*chunk), i.e. file payload bytes minus lo
-              "image": {"offset": lo, "checksums": raw_image.checksums}}
+              "image": {"offset": lo, "total": raw_image.total,
+                        "checksums": raw_image.checksums},
+              # CRC-32C of the windows of THIS file's payload, what a restore
+              # from the file verifies
+              "payload_checksums": _payload_checksums(raw_image, lo, hi)}
     blob = pickle.dumps(header, protocol=4)
     data_off = _round_up(len(MAGIC) + 8 + len(blob), DATA_ALIGN)
     fd = os.open(path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)

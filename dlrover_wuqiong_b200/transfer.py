@@ -462,6 +462,9 @@ class DeviceShardEngine(object):
     def restore_from_device(self, leaves, total, packed, expected=None):
         """Same, but the packed image is a device uint8 tensor (peer recovery)."""
         with torch.cuda.device(self.device):
+            for lf in leaves:
+                if lf.is_cuda and lf.nbytes and not lf.tensor.is_contiguous():
+                    raise ValueError("restore target must be contiguous")
             ptrs, offs, sizes, host = self._sources(leaves)
             plan = self._ensure_plan(ptrs, offs, sizes, total)
             stream = torch.cuda.current_stream(self.device)
@@ -497,11 +500,13 @@ class DeviceShardEngine(object):
         self._arena_pin = None
 
 
-def checksums_to_meta(sums, chunk_bytes, xxh64=None):
+def checksums_to_meta(sums, chunk_bytes, xxh64=None, host_leaves=None):
     entry = {"algo": "crc32c", "chunk_bytes": int(chunk_bytes),
              "sums": np.asarray(sums, dtype=np.uint32).tolist()}
     if xxh64 is not None:
         entry["xxh64"] = list(xxh64)
+    if host_leaves:
+        entry["host_leaves"] = list(host_leaves)
     return entry
 
 

@@ -39,8 +39,9 @@ extern "C" {
 
 #define FCP_VERSION 1
 
-/* work granularity of the kernels: one warp owns one 16 KiB region (32 rows of
- * 512 B); chunk_bytes must be a multiple of it.                              */
+/* work granularity of the kernels: one warp owns one 16 KiB region (16 rows of
+ * 1 KiB, a lane moves one 32-byte word per row); chunk_bytes must be a
+ * multiple of it.                                                           */
 #define FCP_REGION_BYTES 16384u
 #define FCP_DEFAULT_CHUNK_BYTES (2u << 20)
 
@@ -90,7 +91,10 @@ int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
                     uint32_t chunk_bytes, int device, fcp_plan** out);
 /* Refresh the tensor pointers only (same layout), e.g. after the optimizer
  * re-allocated its state; replaces re-walking the dict on later saves
- * (SAVER:281-282).                                                          */
+ * (SAVER:281-282).  Host-side only: the device copy of the table is brought
+ * up to date by the next call that launches kernels for this plan, as an
+ * asynchronous copy from pinned memory on THAT call's stream, so it is
+ * ordered before the kernels on any kind of stream.                         */
 int fcp_plan_update_ptrs(fcp_plan* plan, const void* const* ptrs, uint64_t n);
 void fcp_plan_destroy(fcp_plan* plan);
 uint64_t fcp_plan_total_bytes(const fcp_plan* plan);
@@ -105,6 +109,17 @@ uint64_t fcp_plan_num_regions(const fcp_plan* plan);
  * the segment.  *dev_alias receives the device-side address of `base`.      */
 int fcp_host_register(void* base, uint64_t bytes, void** dev_alias);
 int fcp_host_unregister(void* base);
+
+/* Standard CRC-32C of every window [i*chunk_bytes, min((i+1)*chunk_bytes,
+ * total_bytes)) of a packed image in HOST memory, out[i] per window; the same
+ * values the kernels record (fcp_save_wait, fcp_read_checksums).  Pure host
+ * code — no CUDA call, usable in a process that has no GPU: the agent-side
+ * saver re-checks the shm image with it before persisting (the reference
+ * persists whatever the shm holds, SAVER:914-921), and raw image files get
+ * their per-file sums from it.  SSE4.2 crc32 where the CPU has it, table
+ * slicing otherwise; n_threads <= 0 picks a small default.                  */
+int fcp_host_chunk_crc32c(const void* image, uint64_t total_bytes,
+                          uint32_t chunk_bytes, uint32_t* out, int n_threads);
 
 /* ---- kernels only (packed image already device-addressable) ------------ */
 

@@ -58,6 +58,38 @@ void oracle_chunk_crc32c(const uint8_t* buf, uint64_t total, uint64_t chunk,
   }
 }
 
+/* Same function through the CPU's crc32 instruction (SSE4.2), one serial
+ * stream, so that bench.py can check EVERY chunk of a 19 GB image in seconds;
+ * tests/test_oracle.py checks it against the bytewise statement above.
+ * Returns 0 and leaves `out` alone if the CPU has no SSE4.2. */
+#if defined(__x86_64__)
+#include <nmmintrin.h>
+__attribute__((target("sse4.2"))) static uint32_t crc32c_hw(const uint8_t* p, uint64_t len) {
+  uint64_t c = 0xFFFFFFFFu;
+  while (len && ((uintptr_t)p & 7u)) { c = _mm_crc32_u8((uint32_t)c, *p++); --len; }
+  for (; len >= 8; len -= 8, p += 8) { uint64_t w; memcpy(&w, p, 8); c = _mm_crc32_u64(c, w); }
+  while (len--) c = _mm_crc32_u8((uint32_t)c, *p++);
+  return (uint32_t)c ^ 0xFFFFFFFFu;
+}
+int oracle_chunk_crc32c_hw(const uint8_t* buf, uint64_t total, uint64_t chunk,
+                           uint64_t chunk_begin, uint64_t chunk_end, uint32_t* out) {
+  if (!__builtin_cpu_supports("sse4.2")) return 0;
+  for (uint64_t i = chunk_begin; i < chunk_end; ++i) {
+    uint64_t b = i * chunk;
+    if (b >= total) break;
+    uint64_t n = total - b < chunk ? total - b : chunk;
+    out[i] = crc32c_hw(buf + b, n);
+  }
+  return 1;
+}
+#else
+int oracle_chunk_crc32c_hw(const uint8_t* buf, uint64_t total, uint64_t chunk,
+                           uint64_t chunk_begin, uint64_t chunk_end, uint32_t* out) {
+  (void)buf; (void)total; (void)chunk; (void)chunk_begin; (void)chunk_end; (void)out;
+  return 0;
+}
+#endif
+
 /* -------------------------------------------------------------------- XXH64
  * Restated from the published xxHash specification (XXH64). */
 #define P1 0x9E3779B185EBCA87ULL

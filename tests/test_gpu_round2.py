@@ -1,0 +1,136 @@
+"""GPU: kernel-side robustness added in round 2, through the C ABI.
+
+* the L2 bulk prefetch never asks for bytes beyond the end of a tensor or of
+  the packed image (sources and images placed at the very end of a cudaMalloc
+  allocation);
+* pointer refreshes are uploaded on the launching stream, so they are ordered
+  before the kernels on a non-blocking stream too;
+* the host CRC-32C routine agrees with the sums the pack kernel records.
+"""
+import numpy as np
+import pytest
+import torch
+
+from dlrover_wuqiong_b200 import _native
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+CHUNK = 65536
+
+
+def _raw_alloc(nbytes):
+    """A cudaMalloc'ed range outside torch's caching allocator."""
+    rt = pytest.importorskip("cuda.bindings.runtime")
+    err, ptr = rt.cudaMalloc(nbytes)
+    assert int(err) == 0, err
+    return rt, int(ptr)
+
+
+def _as_tensor(ptr, nbytes):
+    class _Holder(object):
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1",
+                                    "data": (ptr, False), "version": 2}
+    return torch.as_tensor(_Holder(), device="cuda")
+
+
+@pytest.mark.parametrize("mis", [0, 4, 13])
+def test_sources_and_image_at_the_end_of_an_allocation(mis):
+    """Whole-region fast paths with the read side ending exactly where the
+    allocation ends: pack reads a tensor that ends there, scatter reads a
+    packed image that ends there."""
+    torch.cuda.init()
+    size = 4 << 20            # a multiple of the 2 MiB mapping granule
+    n = 3 * 16384 + 16384     # the tensor: four whole regions
+    rt, src = _raw_alloc(size)
+    rt2, img = _raw_alloc(size)
+    try:
+        rng = np.random.default_rng(mis)
+        payload = rng.integers(0, 256, n, dtype=np.uint8)
+        whole_src = _as_tensor(src, size)
+        whole_src.zero_()
+        # source [size - n, size); image offset `mis` makes source and image
+        # misaligned relative to each other (the realigning paths)
+        whole_src[size - n:] = torch.from_numpy(payload).cuda()
+        total = mis + n
+        pad = (total + 16383) // 16384 * 16384
+        whole_img = _as_tensor(img, size)
+        whole_img.fill_(0x5A)
+        packed_ptr = img + size - pad  # the image's padded end == allocation end
+        d = _native.make_descs([src + size - n], [mis], [n])
+        plan = _native.Plan(d, total, 0, CHUNK)
+        stream = torch.cuda.current_stream().cuda_stream
+        plan.pack(packed_ptr, _native.SUM_CRC32C, stream)
+        sums = plan.read_checksums(stream)
+        expect = np.zeros(total, dtype=np.uint8)
+        expect[mis:] = payload
+        got = whole_img[size - pad:size - pad + total].cpu().numpy()
+        assert got.tobytes() == expect.tobytes()
+        assert sums.tolist() == oracle.chunk_crc32c(expect, CHUNK).tolist()
+        # scatter: image of exactly `total` bytes ending at the allocation end
+        if total % 32 == 0:  # keep the image 32-byte aligned for the kernel's loads
+            exact = img + size - total
+            whole_img[size - total:] = torch.from_numpy(expect).cuda()
+        else:
+            exact = packed_ptr
+        out = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        plan.update_ptrs([out.data_ptr()])
+        plan.scatter(exact, _native.SUM_CRC32C, stream)
+        sums2 = plan.read_checksums(stream)
+        assert out.cpu().numpy().tobytes() == payload.tobytes()
+        assert sums2.tolist() == sums.tolist()
+        plan.close()
+        torch.cuda.synchronize()
+    finally:
+        rt.cudaFree(src)
+        rt2.cudaFree(img)
+
+
+def test_pointer_refresh_is_ordered_on_a_non_blocking_stream():
+    """update_ptrs followed by a launch on a non-blocking side stream: the
+    kernels must see the new pointers (the table travels on that stream)."""
+    dev = torch.device("cuda", 0)
+    side = torch.cuda.Stream(device=dev)  # torch side streams are non-blocking
+    n = 1 << 20
+    a = [torch.full((n,), i + 1, dtype=torch.uint8, device=dev) for i in range(8)]
+    b = [torch.full((n,), 101 + i, dtype=torch.uint8, device=dev) for i in range(8)]
+    offs = [i * n for i in range(8)]
+    plan = _native.Plan(_native.make_descs([t.data_ptr() for t in a], offs, [n] * 8),
+                        8 * n, 0, CHUNK)
+    staging = torch.zeros(plan.staging_bytes, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        for rep in range(20):
+            src = b if rep % 2 else a
+            plan.update_ptrs([t.data_ptr() for t in src])
+            plan.pack(staging.data_ptr(), _native.SUM_NONE, side.cuda_stream)
+            side.synchronize()
+            first = staging[::n].cpu().tolist()
+            assert first == [int(t[0]) for t in src], rep
+    plan.close()
+
+
+def test_host_crc_matches_recorded_sums_of_a_save():
+    """Agent-side check: the sums the pack kernel records for an image equal
+    what the host routine computes over the bytes that reached host memory."""
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(5)
+    tensors, offs, sizes, off = [], [], [], 0
+    for _ in range(50):
+        k = int(rng.integers(1, 700000))
+        tensors.append(torch.from_numpy(rng.integers(0, 256, k, dtype=np.uint8)).to(dev))
+        off += int(rng.integers(0, 9))
+        offs.append(off)
+        sizes.append(k)
+        off += k
+    plan = _native.Plan(_native.make_descs([t.data_ptr() for t in tensors], offs, sizes),
+                        off, 0, _native.DEFAULT_CHUNK_BYTES)
+    staging = torch.zeros(plan.staging_bytes, dtype=torch.uint8, device=dev)
+    host = torch.zeros(off, dtype=torch.uint8).pin_memory()
+    stream = torch.cuda.current_stream().cuda_stream
+    plan.save_async(staging.data_ptr(), host.data_ptr(), _native.MODE_STAGED,
+                    _native.SUM_CRC32C, stream)
+    sums = plan.save_wait()
+    got = _native.host_chunk_crc32c(host.data_ptr(), off, _native.DEFAULT_CHUNK_BYTES)
+    assert got.tolist() == sums.tolist()
+    assert got.tolist() == oracle.chunk_crc32c_fast(host.numpy(), _native.DEFAULT_CHUNK_BYTES).tolist()
+    plan.close()

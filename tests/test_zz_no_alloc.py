@@ -18,6 +18,7 @@ import pytest
 import torch
 
 from dlrover_wuqiong_b200 import _native
+from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 CHUNK = 65536
@@ -40,6 +41,16 @@ def _case(seed, n_tensors, max_elems):
     descs = _native.make_descs([t.data_ptr() for t in tensors], offs, sizes)
     descs_dev = torch.from_numpy(descs.view(np.uint8).copy()).to(dev)
     return tensors, descs_dev, len(descs), off
+
+
+def _oracle_image(tensors, descs_dev, total):
+    """What the reference's copy loop leaves in the buffer for this descriptor
+    table (oracle, on host copies of the tensors) and its per-chunk CRC-32C."""
+    host = [t.cpu().numpy() for t in tensors]
+    d = np.frombuffer(descs_dev.cpu().numpy().tobytes(), dtype=_native.DESC_DTYPE).copy()
+    d["ptr"] = [h.ctypes.data for h in host]
+    image = oracle.pack_descs(d.view(oracle.DESC_DTYPE), total)
+    return image, oracle.chunk_crc32c(image, CHUNK)
 
 
 def _run(entry, descs_dev, n, total, direction, packed):
@@ -75,6 +86,11 @@ def test_noalloc_matches_existing_entry_point_twice_in_a_row():
         sums_b = _run("noalloc", descs_dev, n, total, 0, packed_b)
         assert torch.equal(packed_a[:total], packed_b[:total])
         assert sums_a.tolist() == sums_b.tolist()
+        # and both against the oracle, so this is not the CUDA path checked
+        # against itself
+        want_image, want_sums = _oracle_image(tensors, descs_dev, total)
+        assert packed_b[:total].cpu().numpy().tobytes() == want_image.tobytes()
+        assert sums_b.tolist() == want_sums.tolist()
         # scatter direction: unpack image b into fresh tensors
         fresh = [torch.zeros_like(t) for t in tensors]
         d = np.frombuffer(descs_dev.cpu().numpy().tobytes(), dtype=_native.DESC_DTYPE).copy()
