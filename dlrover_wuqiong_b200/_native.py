@@ -54,6 +54,9 @@ SYMBOLS = [
     ("fcp_restore", _i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
     ("fcp_restore_bounced", _i, [_vp, _vp, _vp, _i, _vp, _i, _vp]),
     ("fcp_restore_from_device", _i, [_vp, _vp, _i, _vp, _vp]),
+    ("fcp_restore_from_slices", _i, [_vp, _vp, _u64, _u64, _i, _vp, _i, _vp]),
+    ("fcp_stage_range", _i, [_vp, _vp, _vp, _u64, _u64, _i, _i, _vp]),
+    ("fcp_plan_set_window", _i, [_vp, _u64, _u64]),
     ("fcp_plan_timings", _i, [_vp, _vp]),
     ("fcp_plan_last_launches", _u64, [_vp]),
     ("fcp_plan_set_copy_piece_bytes", _i, [_vp, _u64]),
@@ -187,6 +190,28 @@ class Plan:
         check(lib().fcp_restore_from_device(
             self._h, packed_ptr, checksum,
             exp.ctypes.data if exp is not None else None, stream))
+
+    def restore_from_slices(self, bases, slice_bytes, checksum=SUM_CRC32C, expected=None,
+                            read_prefetch=False, stream=0):
+        """bases[s]: address image byte 0 would have in the buffer that holds
+        slice s (see fcp.h)."""
+        a = np.ascontiguousarray(bases, dtype=np.uint64)
+        exp = None
+        if expected is not None:
+            exp = np.ascontiguousarray(expected, dtype=np.uint32)
+            if len(exp) != self.num_chunks:
+                raise ValueError("expected %d checksums, got %d" % (self.num_chunks, len(exp)))
+        check(lib().fcp_restore_from_slices(
+            self._h, a.ctypes.data, len(a), slice_bytes, checksum,
+            exp.ctypes.data if exp is not None else None, 1 if read_prefetch else 0, stream))
+
+    def stage_range(self, host_ptr, staging_ptr, byte_begin, byte_end, registered=False,
+                    n_workers=0, stream=0):
+        check(lib().fcp_stage_range(self._h, host_ptr, staging_ptr, byte_begin, byte_end,
+                                    1 if registered else 0, n_workers, stream))
+
+    def set_window(self, chunk_begin=0, chunk_end=0xFFFFFFFFFFFFFFFF):
+        check(lib().fcp_plan_set_window(self._h, chunk_begin, chunk_end))
 
     def timings(self):
         out = (ctypes.c_float * 3)()

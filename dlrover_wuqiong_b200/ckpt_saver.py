@@ -161,6 +161,9 @@ class PendingSave(object):
         self._engine = engine
         self._host_leaves = host_leaves  # layout indices of host-resident leaves
         self._done = False
+        self._transferred = False
+        self._sums = None
+        self.window = None  # (chunk_begin, chunk_end) of a striped save
 
     def wait_packed(self):
         """Return once the live tensors may be modified again."""
@@ -171,22 +174,43 @@ class PendingSave(object):
         """Return once the shm holds the complete shard and the meta says so."""
         if self._done:
             return
+        self.publish(self.wait_transfer())
+
+    def wait_transfer(self):
+        """Return once this rank's bytes are in the shm; -> its chunk sums (a
+        value per chunk of the image; for a striped save only those of
+        ``window`` mean anything), None if there are none."""
+        if self._transferred:
+            return self._sums
+        self._transferred = True
+        if self._engine is not None:
+            self._sums = self._engine.save_finish()
+            self._handler.last_stats = dict(self._engine.stats)
+        return self._sums
+
+    def publish(self, sums):
+        """Record `sums` (of the WHOLE image) in the meta and tell the agent
+        the image is complete (writing_shm=False).  Owner of the segment only."""
+        if self._done:
+            return
         self._done = True
         h = self._handler
-        if self._engine is not None:
-            sums = self._engine.save_finish()
-            h.last_stats = dict(self._engine.stats)
-            if sums is not None:
-                from .transfer import checksums_to_meta
-                self._meta[FCP_CHECKSUM_KEY] = checksums_to_meta(
-                    sums, self._engine.chunk_bytes, self._engine.stats.get("xxh64"),
-                    host_leaves=self._host_leaves)
-            else:
-                self._meta.pop(FCP_CHECKSUM_KEY, None)
+        if sums is not None:
+            from .transfer import checksums_to_meta
+            self._meta[FCP_CHECKSUM_KEY] = checksums_to_meta(
+                sums, self._engine.chunk_bytes, self._engine.stats.get("xxh64"),
+                host_leaves=self._host_leaves)
         else:
             self._meta.pop(FCP_CHECKSUM_KEY, None)
         self._conf.writing_shm = False
         h._publish(self._meta, self._conf)
+        h._note_staged(self._conf.step if self._engine is not None else 0, self.window)
+
+    def abandon(self, step):
+        """A rank that wrote one stripe of another rank's segment: nothing to
+        publish; remember what its HBM staging now holds."""
+        self._done = True
+        self._handler._note_staged(step if self._engine is not None else 0, self.window)
 
 
 class SharedMemoryHandler(object):
@@ -214,9 +238,33 @@ class SharedMemoryHandler(object):
         self._delta_ok = False  # the agent holds the meta tree of the current layout
         self._changes = []      # non-tensor leaves refreshed by the current save
         self.last_stats = {}
+        # what the engine's HBM staging holds: (step, byte_lo, byte_hi) of a
+        # complete, checksummed image (or stripe of one); step 0 = nothing
+        self._staged = (0, 0, 0)
 
     # -- lifecycle ----------------------------------------------------------
+    def _note_staged(self, step, window=None):
+        eng = self._engine
+        if eng is None or eng.staging is None or not step:
+            self._staged = (0, 0, 0)
+            return
+        total = self._buffer_size
+        if window is None:
+            self._staged = (step, 0, total)
+        else:
+            self._staged = (step, window[0] * eng.chunk_bytes,
+                            min(total, window[1] * eng.chunk_bytes))
+
+    def staged_image(self):
+        """(step, byte_lo, byte_hi): the part of the checkpoint image of `step`
+        that this process still holds, complete, in HBM staging — the source
+        of peer recovery over NVLink.  (0, 0, 0) if none."""
+        if self._engine is None or self._engine.staging is None:
+            return (0, 0, 0)
+        return self._staged
+
     def _drop_engine(self):
+        self._staged = (0, 0, 0)
         if self._engine is not None:
             self._engine.close()  # also drops the pinned mapping of the segment
             self._engine = None
@@ -290,10 +338,11 @@ class SharedMemoryHandler(object):
         self.metadata.set(meta_dict)
         self._delta_ok = os.getenv("FCP_META_DELTA", "1") == "1"
 
-    def _layout_for(self, state_dict):
+    def _layout_for(self, state_dict, create=True):
         """(meta_dict, leaves) for this save: the cached layout if the dict
         still has the same structure, a fresh one (and a fresh segment of the
-        exact size) otherwise."""
+        exact size) otherwise.  create=False: this rank writes a stripe of a
+        segment another rank owns — attach to it, never create."""
         if self.shared_memory is not None:
             meta_dict = self.metadata.get(local=True)
             if meta_dict:
@@ -307,6 +356,21 @@ class SharedMemoryHandler(object):
         meta_dict, leaves, total = _plan.build_layout(state_dict)
         self._buffer_size = total
         self._n_metas = len(leaves)
+        if not create:
+            if self.shared_memory is None or self.shared_memory.size != total \
+                    or self._segment_replaced():
+                if self.shared_memory is not None:
+                    self._drop_engine()
+                    self.shared_memory.close()
+                self.init_shared_memory(create=False)
+            if self.shared_memory is None or self.shared_memory.size != total:
+                raise RuntimeError("the segment %s of the stripe owner has %s bytes, this "
+                                   "rank's state needs %d: replicas differ"
+                                   % (self._shm_name, getattr(self.shared_memory, "size", None),
+                                      total))
+            # the owner's meta is the one the agent gets; keep ours locally
+            self.metadata._dict = meta_dict
+            return meta_dict, leaves
         if self.shared_memory is None or self.shared_memory.size != total:
             if self.shared_memory is not None:
                 self._drop_engine()
@@ -326,7 +390,17 @@ class SharedMemoryHandler(object):
                 return self._engine
         return None
 
-    def save_state_dict_async(self, state_dict):
+    def save_state_dict_async(self, state_dict, stripe=None, attach_barrier=None):
+        """`stripe` = (index, count, owner): this rank moves stripe `index` of
+        `count` of an image that every rank of a replicated group holds
+        identically, into ONE segment; `owner` (exactly one rank) creates the
+        segment and talks to the agent.  `attach_barrier()`: called by every
+        rank between the owner's (re)creation of the segment + its
+        writing_shm=True announcement and the first write of any rank.
+        CUDA tensors only."""
+        if stripe is not None:
+            return self._save_stripe_async(state_dict, stripe, attach_barrier)
+        self._staged = (0, 0, 0)
         meta_dict, leaves = self._layout_for(state_dict)
         conf = meta_dict.get(DLROVER_CKPT_CONFIG_KEY)
         if conf is None:
@@ -352,6 +426,34 @@ class SharedMemoryHandler(object):
         self._wait_populated()
         _host_copy_leaves(leaves, self.shared_memory.buf)
         return PendingSave(self, meta_dict, conf, None)
+
+    def _save_stripe_async(self, state_dict, stripe, attach_barrier):
+        index, count, owner = stripe
+        self._staged = (0, 0, 0)
+        meta_dict = leaves = conf = None
+        if owner:
+            meta_dict, leaves = self._layout_for(state_dict)
+            conf = meta_dict.get(DLROVER_CKPT_CONFIG_KEY)
+            if conf is None:
+                conf = meta_dict[DLROVER_CKPT_CONFIG_KEY] = CheckpointConfig()
+            conf.writing_shm = True
+            self._announce(meta_dict, conf)
+        if attach_barrier is not None:
+            attach_barrier()
+        if not owner:
+            meta_dict, leaves = self._layout_for(state_dict, create=False)
+            conf = meta_dict.get(DLROVER_CKPT_CONFIG_KEY) or CheckpointConfig()
+        engine = self._engine_for(leaves)
+        if engine is None or self.shared_memory is None:
+            raise ValueError("striped saves need a state dict with CUDA tensors")
+        window = engine.stripe_of(self._buffer_size, index, count)
+        engine.save_begin(leaves, self._buffer_size, self.shared_memory.buf,
+                          ready=getattr(self.shared_memory, "wait_populated", None)
+                          if owner else None, window=window)
+        host_leaves = [i for i, lf in enumerate(leaves) if not lf.is_cuda]
+        pending = PendingSave(self, meta_dict, conf, engine, host_leaves)
+        pending.window = window
+        return pending
 
     def save_state_dict(self, state_dict):
         """Copy the state dict into the shm segment; complete on return
@@ -423,6 +525,10 @@ class SharedMemoryHandler(object):
                            expected_xxh64=(entry or {}).get("xxh64") if expected is not None
                            else None)
             self.last_stats = dict(engine.stats)
+            # the staging now holds the verified image: this rank can serve it
+            self._buffer_size = total
+            conf = meta_dict.get(DLROVER_CKPT_CONFIG_KEY)
+            self._note_staged(conf.step if conf is not None and expected is not None else 0)
         else:
             for lf in leaves:
                 if lf.nbytes:

@@ -95,7 +95,7 @@ constexpr int kSmallThreads = 256;
 constexpr size_t kSmemBig = sizeof(uint32_t) * (1024 * 32 + 1024 * 16 + 5120);
 constexpr size_t kSmemSmall = sizeof(uint32_t) * (1024 + 1024 + 5120);
 
-template <bool PACK, bool CRC>
+template <bool PACK, bool CRC, bool SLICED = false>
 int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
   fcpk::Args a = a_in;
   const uint64_t regions = a.region_end - a.region_begin;
@@ -114,8 +114,14 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
   const uint64_t runs = ceil_div(regions, a.run);
   const bool big = (CRC || force_big) && runs >= static_cast<uint64_t>(sms) * 32;
   if (big) {
-    auto kern = fcpk::fcp_kernel<PACK, CRC, 32, kBigThreads>;
+    auto kern = fcpk::fcp_kernel<PACK, CRC, 32, kBigThreads, SLICED>;
     if (!g_attr_done[dev]) {
+      FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<false, true, 32, kBigThreads, true>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBig));
+      FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<false, false, 32, kBigThreads, true>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBig));
       FCP_CUDA(cudaFuncSetAttribute(fcpk::fcp_kernel<true, true, 32, kBigThreads>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kSmemBig));
@@ -132,7 +138,7 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
     }
     kern<<<sms, kBigThreads, kSmemBig, st>>>(a);
   } else {
-    auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads>;
+    auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads, SLICED>;
     const uint64_t want = ceil_div(runs, kSmallThreads / 32);
     const uint64_t cap = static_cast<uint64_t>(sms) * 8;
     const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
@@ -144,6 +150,11 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
 
 int launch_any(const fcpk::Args& a, int direction, int checksum, int dev,
                cudaStream_t st) {
+  if (a.slice_base != nullptr) {  // scatter only
+    if (direction != 1) return fail(-EINVAL, "a sliced image can only be scattered");
+    return checksum ? launch_dir<false, true, true>(a, dev, st)
+                    : launch_dir<false, false, true>(a, dev, st);
+  }
   if (direction == 0)
     return checksum ? launch_dir<true, true>(a, dev, st)
                     : launch_dir<true, false>(a, dev, st);
@@ -205,6 +216,9 @@ struct fcp_plan {
   bool last_has_sums = false;
   bool save_in_flight = false;
   int save_mode = 0;
+  uint64_t win_begin = 0, win_end = ~0ull;  // chunk window of fcp_save_async
+  const uint8_t** d_slice_bases = nullptr;  // table of fcp_restore_from_slices
+  uint64_t slice_bases_cap = 0;
   // pinned bounce ring of fcp_restore_bounced: 2 slots per worker
   uint8_t* ring = nullptr;
   uint64_t ring_slot_bytes = 0;
@@ -302,10 +316,14 @@ int copy_image_range(fcp_plan* p, uint8_t* dev, uint8_t* host, uint64_t b0,
 // 8 GiB ones); a restore runs the schedule backwards so only a small scatter
 // trails the last DMA.
 std::vector<std::pair<uint64_t, uint64_t>> make_slices(const fcp_plan* p,
-                                                       bool growing) {
+                                                       bool growing,
+                                                       uint64_t first = 0,
+                                                       uint64_t last = ~0ull) {
   std::vector<uint64_t> sizes;
   const uint64_t cps0 = p->slice_bytes / p->chunk_bytes;
-  uint64_t left = p->n_chunks, cur = cps0 ? cps0 : 1;
+  if (last > p->n_chunks) last = p->n_chunks;
+  if (first > last) first = last;
+  uint64_t left = last - first, cur = cps0 ? cps0 : 1;
   while (left) {
     const uint64_t take = cur < left ? cur : left;
     sizes.push_back(take);
@@ -314,7 +332,7 @@ std::vector<std::pair<uint64_t, uint64_t>> make_slices(const fcp_plan* p,
   }
   if (!growing) std::reverse(sizes.begin(), sizes.end());
   std::vector<std::pair<uint64_t, uint64_t>> out;
-  uint64_t at = 0;
+  uint64_t at = first;
   for (uint64_t sz : sizes) {
     out.emplace_back(at, at + sz);
     at += sz;
@@ -454,6 +472,7 @@ void fcp_plan_destroy(fcp_plan* p) {
   if (p->h_pinned) cudaFreeHost(p->h_pinned);
   if (p->ev_upload) cudaEventDestroy(p->ev_upload);
   if (p->ring) cudaFreeHost(p->ring);
+  if (p->d_slice_bases) cudaFree(p->d_slice_bases);
   if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
   cudaEvent_t evs[] = {p->ev_begin, p->ev_packed, p->ev_done, p->ev_kern_b,
                        p->ev_kern_e};
@@ -717,6 +736,8 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
   FCP_CUDA(cudaEventRecord(p->ev_begin, st));
   p->last_launches = 0;
   if (mode == FCP_MODE_DIRECT) {
+    if (p->win_begin != 0 || p->win_end < p->n_chunks)
+      return fail(-EINVAL, "a chunk window needs a staged mode");
     void* alias = nullptr;
     FCP_CUDA(cudaHostGetDevicePointer(&alias, host_dst, 0));
     rc = plan_launch(p, alias, 0, checksum, 0, p->n_chunks, st);
@@ -734,7 +755,7 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
         return fail(-ENOTSUP, "host pointer is not usable from the device as is");
       host_alias = static_cast<uint8_t*>(a0);
     }
-    const auto slices = make_slices(p, true);
+    const auto slices = make_slices(p, true, p->win_begin, p->win_end);
     rc = plan_slice_events(p, slices.size());
     if (rc) return rc;
     for (size_t s = 0; s < slices.size(); ++s) {
@@ -763,9 +784,11 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
     // the sources are free once the last pack kernel is done; combining the
     // region values into chunk values only touches the plan's own buffers
     FCP_CUDA(cudaEventRecord(p->ev_packed, st));
-    if (checksum && p->n_chunks) {
+    const uint64_t wb = p->win_begin < p->n_chunks ? p->win_begin : p->n_chunks;
+    const uint64_t we = p->win_end < p->n_chunks ? p->win_end : p->n_chunks;
+    if (checksum && we > wb) {
       rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
-                           p->chunk_bytes / FCP_REGION_BYTES, 0, p->n_chunks, st);
+                           p->chunk_bytes / FCP_REGION_BYTES, wb, we, st);
       if (rc) return rc;
       p->last_launches++;
       FCP_CUDA(cudaEventRecord(p->ev_kern_e, st));
@@ -913,15 +936,10 @@ int fcp_restore_from_device(fcp_plan* p, const void* packed, int checksum,
   return 0;
 }
 
-int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
-                        int checksum, const uint32_t* expected, int n_workers,
-                        void* stream) {
-  if (!p) return fail(-EINVAL, "plan is NULL");
-  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
-  if ((!host_src || !staging) && p->total)
-    return fail(-EINVAL, "host_src and staging are required");
-  if (expected && !checksum)
-    return fail(-EINVAL, "expected sums given but checksum disabled");
+// Copy image bytes [b0, b1) from an UNPINNED host image into `staging`
+// through the plan's pinned ring, n_workers host threads; synchronous.
+static int bounce_range(fcp_plan* p, const void* host_src, void* staging,
+                        uint64_t b0, uint64_t b1, int n_workers) {
   if (n_workers <= 0) {
     unsigned hc = std::thread::hardware_concurrency();
     n_workers = hc >= 16 ? 8 : hc >= 4 ? static_cast<int>(hc / 2) : 1;
@@ -944,21 +962,15 @@ int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
     p->ring_workers = n_workers;
     p->ring_slot_bytes = slot;
   }
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  {
-    int rc0 = plan_sync_descs(p, st);
-    if (rc0) return rc0;
-  }
-  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
-  FCP_CUDA(cudaStreamSynchronize(st));  // staging is free, caller's work done
-  const uint64_t n_slices = ceil_div(p->total, slot);
+  if (b1 <= b0) return 0;
+  const uint64_t n_slices = ceil_div(b1 - b0, slot);
   std::atomic<uint64_t> next{0};
   std::atomic<int> failed{0};
-  const uint8_t* src = static_cast<const uint8_t*>(host_src);
-  uint8_t* dst = static_cast<uint8_t*>(staging);
+  const uint8_t* src = static_cast<const uint8_t*>(host_src) + b0;
+  uint8_t* dst = static_cast<uint8_t*>(staging) + b0;
   const int device = p->device;
   uint8_t* ring = p->ring;
-  const uint64_t total = p->total;
+  const uint64_t total = b1 - b0;
   auto worker = [&, device, ring, total](int w) {
     if (cudaSetDevice(device) != cudaSuccess) { failed = 1; return; }
     cudaStream_t ws = nullptr;
@@ -999,8 +1011,29 @@ int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
     cudaGetLastError();
     return fail(-EIO, "bounced host->device copy failed");
   }
+  return 0;
+}
+
+int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
+                        int checksum, const uint32_t* expected, int n_workers,
+                        void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
+  if ((!host_src || !staging) && p->total)
+    return fail(-EINVAL, "host_src and staging are required");
+  if (expected && !checksum)
+    return fail(-EINVAL, "expected sums given but checksum disabled");
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = plan_sync_descs(p, st);
+  if (rc) return rc;
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  FCP_CUDA(cudaStreamSynchronize(st));  // staging is free, caller's work done
+  rc = bounce_range(p, host_src, staging, 0, p->total, n_workers);
+  if (rc) return rc;
   p->last_launches = 0;
-  int rc = plan_launch(p, staging, 1, checksum, 0, p->n_chunks, st);
+  rc = plan_launch(p, staging, 1, checksum, 0, p->n_chunks, st);
   if (rc) return rc;
   if (checksum && p->n_chunks)
     FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
@@ -1010,6 +1043,113 @@ int fcp_restore_bounced(fcp_plan* p, const void* host_src, void* staging,
   FCP_CUDA(cudaEventSynchronize(p->ev_done));
   FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
   p->t_kernel_ms = 0.f;
+  p->t_copy_ms = 0.f;
+  p->last_has_sums = checksum != 0;
+  if (expected) return verify_sums(p, expected);
+  return 0;
+}
+
+int fcp_plan_set_window(fcp_plan* p, uint64_t chunk_begin, uint64_t chunk_end) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
+  if (chunk_begin > chunk_end) return fail(-EINVAL, "bad chunk window");
+  p->win_begin = chunk_begin;
+  p->win_end = chunk_end;
+  return 0;
+}
+
+int fcp_stage_range(fcp_plan* p, const void* host_src, void* staging,
+                    uint64_t byte_begin, uint64_t byte_end, int registered,
+                    int n_workers, void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
+  if (byte_end > p->total) byte_end = p->total;
+  if (byte_begin >= byte_end) return 0;
+  if (!host_src || !staging) return fail(-EINVAL, "host_src and staging are required");
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  FCP_CUDA(cudaStreamSynchronize(st));  // the staging range is free
+  int rc = 0;
+  if (registered) {
+    rc = copy_image_range(p, static_cast<uint8_t*>(staging),
+                          const_cast<uint8_t*>(static_cast<const uint8_t*>(host_src)),
+                          byte_begin, byte_end, false, p->copy_stream);
+    if (rc) return rc;
+    FCP_CUDA(cudaStreamSynchronize(p->copy_stream));
+  } else {
+    rc = bounce_range(p, host_src, staging, byte_begin, byte_end, n_workers);
+    if (rc) return rc;
+  }
+  FCP_CUDA(cudaEventRecord(p->ev_done, st));
+  FCP_CUDA(cudaEventSynchronize(p->ev_done));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
+  p->t_copy_ms = p->t_total_ms;
+  p->t_kernel_ms = 0.f;
+  p->last_launches = 0;
+  return 0;
+}
+
+int fcp_restore_from_slices(fcp_plan* p, const void* const* slice_bases,
+                            uint64_t n_slices, uint64_t slice_bytes, int checksum,
+                            const uint32_t* expected, int read_prefetch,
+                            void* stream) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (expected && !checksum)
+    return fail(-EINVAL, "expected sums given but checksum disabled");
+  if (slice_bytes == 0 || slice_bytes % FCP_REGION_BYTES != 0)
+    return fail(-EINVAL, "slice_bytes must be a positive multiple of %u", FCP_REGION_BYTES);
+  if (!slice_bases || n_slices < ceil_div(p->total, slice_bytes))
+    return fail(-EINVAL, "%llu slices of %llu bytes do not cover the image",
+                (unsigned long long)n_slices, (unsigned long long)slice_bytes);
+  if (slice_bytes / FCP_REGION_BYTES > 0xFFFFFFFFull)
+    return fail(-EINVAL, "slice_bytes too large");
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = plan_sync_descs(p, st);
+  if (rc) return rc;
+  if (p->slice_bases_cap < n_slices) {
+    if (p->d_slice_bases) cudaFree(p->d_slice_bases);
+    p->d_slice_bases = nullptr;
+    p->slice_bases_cap = 0;
+    if (cudaMalloc(&p->d_slice_bases, sizeof(void*) * n_slices) != cudaSuccess) {
+      cudaGetLastError();
+      return fail(-ENOMEM, "cannot allocate the slice table");
+    }
+    p->slice_bases_cap = n_slices;
+  }
+  // pageable source: staged by the runtime before the call returns, then
+  // ordered on `st` before the kernels
+  FCP_CUDA(cudaMemcpyAsync(p->d_slice_bases, slice_bases, sizeof(void*) * n_slices,
+                           cudaMemcpyHostToDevice, st));
+  FCP_CUDA(cudaEventRecord(p->ev_begin, st));
+  p->last_launches = 0;
+  const uint32_t rpc = p->chunk_bytes / FCP_REGION_BYTES;
+  if (p->n_regions) {
+    fcpk::Args a = plan_args(p, nullptr, 0, p->n_regions);
+    a.slice_base = p->d_slice_bases;
+    a.slice_regions = static_cast<uint32_t>(slice_bytes / FCP_REGION_BYTES);
+    if (!read_prefetch) a.flags |= fcpk::kNoPrefetch;
+    rc = launch_any(a, 1, checksum, p->device, st);
+    if (rc) return rc;
+    p->last_launches++;
+    if (checksum) {
+      rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions, rpc, 0,
+                           p->n_chunks, st);
+      if (rc) return rc;
+      p->last_launches++;
+    }
+  }
+  if (checksum && p->n_chunks)
+    FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                             sizeof(uint32_t) * p->n_chunks,
+                             cudaMemcpyDeviceToHost, st));
+  FCP_CUDA(cudaEventRecord(p->ev_done, st));
+  FCP_CUDA(cudaEventSynchronize(p->ev_done));
+  FCP_CUDA(cudaEventElapsedTime(&p->t_total_ms, p->ev_begin, p->ev_done));
+  p->t_kernel_ms = p->t_total_ms;
   p->t_copy_ms = 0.f;
   p->last_has_sums = checksum != 0;
   if (expected) return verify_sums(p, expected);

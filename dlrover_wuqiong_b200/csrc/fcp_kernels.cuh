@@ -280,6 +280,13 @@ struct Args {
   uint32_t run;    // regions per warp visit, set by the launcher
   uint32_t flags;  // kNoPrefetch: the read side is peer memory (never in local L2)
   uint32_t* work;  // two zeroed counters for dynamic run distribution, or nullptr
+  // Scatter from an image whose pieces live in several buffers (peers' HBM):
+  // region r is read through slice_base[r / slice_regions] instead of
+  // `packed`.  Every entry is the address image byte 0 WOULD have in that
+  // buffer (so absolute offsets apply); the buffer only has to hold the bytes
+  // of the slices that point at it (a region never reads outside itself).
+  const uint8_t* const* slice_base = nullptr;  // device array, or nullptr
+  uint32_t slice_regions = 0;
 };
 constexpr uint32_t kNoPrefetch = 1u;
 

@@ -113,7 +113,10 @@ __device__ __forceinline__ void store_some_bytes(uintptr_t t, const W8& w, int f
 // PACK = false: packed image -> tensors   (desc.ptr is the target)
 // REPL: replication of the 4-byte update table in shared memory (1 or 32);
 // the row-shift table is replicated REPL/2 ways.
-template <bool PACK, bool CRC, int REPL, int THREADS>
+// SLICED: the image is read through Args.slice_base (scatter from several
+// buffers); a separate instantiation so the ordinary kernels keep their
+// register budget.
+template <bool PACK, bool CRC, int REPL, int THREADS, bool SLICED = false>
 __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   constexpr int RK = REPL > 1 ? REPL / 2 : 1;
   constexpr int kBatch = FCP_ALIGNED_BATCH;
@@ -169,6 +172,12 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
    cur_load(c, descs, n);
    for (uint64_t r = run_begin; r < run_end; ++r) {
     const uint64_t rbase = r * kRegion;
+    // where this region of the image is read from / written to
+    uint8_t* const pk = !SLICED
+        ? a.packed
+        : reinterpret_cast<uint8_t*>(static_cast<uintptr_t>(__ldg(
+              reinterpret_cast<const unsigned long long*>(a.slice_base) +
+              r / a.slice_regions)));
     cur_seek(c, descs, n, rbase);  // same answer in every lane
     uint32_t acc = 0;
     const uint64_t lane_o = rbase + static_cast<uint64_t>(lane) * kWordBytes;
@@ -178,17 +187,17 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
     const bool whole = (c.off <= rbase) && (rbase + kRegion <= c.end);
     if (whole) {
       const uintptr_t t0 = c.ptr + (rbase - c.off) + lane * kWordBytes;  // tensor side
-      uint8_t* p0 = a.packed + lane_o;                                   // packed side
+      uint8_t* p0 = pk + lane_o;                                   // packed side
       const uint32_t mis = static_cast<uint32_t>(t0 & 31u);
       // read side of this region, seen by lane 0 (16-byte aligned down): the
       // batch after the one being loaded is prefetched into L2 by one bulk
       // request, so the 256-bit loads mostly hit L2 instead of waiting on HBM
       const uintptr_t rd0 = (PACK ? c.ptr + (rbase - c.off)
-                                  : reinterpret_cast<uintptr_t>(a.packed + rbase)) & ~uintptr_t(15);
+                                  : reinterpret_cast<uintptr_t>(pk + rbase)) & ~uintptr_t(15);
       // where the read side ends: the prefetch of the last batch reaches a few
       // bytes past the region and must not leave the tensor / the image
       const uintptr_t rd_lim = PACK ? c.ptr + (c.end - c.off)
-                                    : reinterpret_cast<uintptr_t>(a.packed) + total;
+                                    : reinterpret_cast<uintptr_t>(pk) + total;
       if (PACK && mis != 0) {
         // source not 32-byte aligned relative to the image: fetch the two
         // aligned words around each word (the second is the next lane's
@@ -293,13 +302,13 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
                 const W8 hi = ld32(reinterpret_cast<const void*>(t - mis + kWordBytes));
                 v = extract32(lo, hi, mis);
               }
-              st32(a.packed + o, v);
+              st32(pk + o, v);
             } else {
               v = gather_word(c, descs, n, o, total);
-              store_packed(a.packed, o, total, v);
+              store_packed(pk, o, total, v);
             }
           } else {
-            v = load_packed(a.packed, o, total);
+            v = load_packed(pk, o, total);
             if (interior)
               st32_unaligned(c.ptr + (o - c.off), v);
             else

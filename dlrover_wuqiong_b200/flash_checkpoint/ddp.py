@@ -23,6 +23,13 @@ class DdpCheckpointer(Checkpointer):
         replica_count (int): in-memory replicas on other nodes.
         async_save (bool): return from save as soon as the tensors are
             snapshotted in HBM (extension; default off = reference semantics).
+        stripe_replicas (bool): replicated state (global_shard_num == 1) on a
+            GPU job: EVERY local rank calls save_checkpoint and writes 1/n of
+            the node's one image over its own host link, instead of local rank
+            0 writing all of it (extension; default off, or FCP_STRIPE_REPLICAS=1).
+            Restores of replicated state fetch 1/n per rank and exchange the
+            stripes over NVLink whenever ``load_checkpoint`` is given ``into=``
+            or ``device=`` (FCP_PEER_RESTORE=0 switches that off).
 
     Example::
 
@@ -39,7 +46,7 @@ class DdpCheckpointer(Checkpointer):
     def __init__(self, checkpoint_dir: str, local_shard_num=1, global_shard_num=1,
                  comm_backend="", deletion_strategy=None,
                  save_timeout=CheckpointConstant.SAVE_TIMEOUT, replica_count=0,
-                 async_save=None):
+                 async_save=None, stripe_replicas=None):
         self.checkpoint_dir = checkpoint_dir
         self._rank = dist.get_rank() if dist.is_initialized() else 0
         self.storage = get_checkpoint_storage(deletion_strategy)
@@ -47,7 +54,8 @@ class DdpCheckpointer(Checkpointer):
             checkpoint_dir=checkpoint_dir, storage=self.storage,
             local_shard_num=local_shard_num, global_shard_num=global_shard_num,
             comm_backend=comm_backend, save_timeout=save_timeout,
-            replica_count=replica_count, async_save=async_save)
+            replica_count=replica_count, async_save=async_save,
+            stripe_replicas=stripe_replicas)
 
     def save_checkpoint(self, step, state_dict, path="", storage_type=StorageType.DISK):
         if path == "":

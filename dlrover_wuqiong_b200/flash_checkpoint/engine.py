@@ -133,7 +133,7 @@ class CheckpointEngine(metaclass=ABCMeta):
 
     def __init__(self, checkpoint_dir: str, storage: CheckpointStorage, comm_backend: str = "",
                  save_timeout: int = CheckpointConstant.SAVE_TIMEOUT, replica_count=0,
-                 async_save=None):
+                 async_save=None, stripe_replicas=None):
         if not self.saver_proc:
             self.saver_proc = start_saver_process()
         self.checkpoint_dir = checkpoint_dir
@@ -145,6 +145,11 @@ class CheckpointEngine(metaclass=ABCMeta):
         if async_save is None:
             async_save = os.getenv("FCP_ASYNC_SAVE", "0") == "1"
         self._async_save = async_save
+        if stripe_replicas is None:
+            stripe_replicas = os.getenv("FCP_STRIPE_REPLICAS", "0") == "1"
+        self._stripe_replicas = bool(stripe_replicas)
+        self._node_group = None   # gloo group of this node's ranks (striped saves)
+        self._node_ranks: List[int] = []
         self._finisher: Optional[threading.Thread] = None
         # only local rank 0 talks to the agent's event queue
         self._event_queue = SharedQueue(
@@ -162,6 +167,7 @@ class CheckpointEngine(metaclass=ABCMeta):
         self._saver_group = None
         self._saving_ranks: Optional[List[int]] = None
         self._init_sync_group(comm_backend)
+        self._init_node_group()
         self._notify_agent_to_create_saver()
         self._update_saver_config()
         self._replica_manager = CkptReplicaManger.create_replica_manager(
@@ -192,6 +198,29 @@ class CheckpointEngine(metaclass=ABCMeta):
                 self._local_rank,
                 "Create a %s communication group to save checkpoint. Saving ranks are %s."
                 % (backend, self._saving_ranks or "all ranks"))
+
+    def _striping(self):
+        """Striped saves: replicated state (one global shard), several ranks
+        per node, CUDA.  Every local rank then writes 1/n of the ONE image of
+        its node over its own host link."""
+        return (self._stripe_replicas and self._node_group is not None
+                and len(self._node_ranks) > 1 and torch.cuda.is_available())
+
+    def _init_node_group(self):
+        if not (self._stripe_replicas and dist.is_initialized()
+                and self.get_global_shard_num() == 1):
+            return
+        per_node = env_utils.get_local_world_size()
+        world = dist.get_world_size()
+        if per_node < 2 or world % per_node:
+            return
+        # small CPU collectives (chunk sums, the pre-write barrier), also from
+        # the finisher thread of an async save: gloo, apart from the NCCL group
+        for node in range(world // per_node):
+            ranks = list(range(node * per_node, (node + 1) * per_node))
+            group = dist.new_group(ranks=ranks, backend="gloo", timeout=timedelta(seconds=300))
+            if self._rank in ranks:
+                self._node_group, self._node_ranks = group, ranks
 
     def __del__(self):
         try:
@@ -243,6 +272,8 @@ class CheckpointEngine(metaclass=ABCMeta):
         get its shm lock because the agent is still persisting the previous
         checkpoint — training is never blocked on the saver (ENGINE:297-330).
         """
+        if self._striping():
+            return self._save_striped(state_dict, conf)
         if self._local_rank != self.local_shard_id:
             return False
         if self._saving_ranks and self._rank not in self._saving_ranks:
@@ -284,7 +315,95 @@ class CheckpointEngine(metaclass=ABCMeta):
         self._replica_manager.backup(self._shm_handler)
         return True
 
+    def _save_striped(self, state_dict, conf: CheckpointConfig):
+        """Replicated state, every local rank takes part (all of them must call
+        save with the same state): the owner — the rank that would have saved
+        alone (full_ckpt_engine.py:75-88) — takes the lock, owns the segment
+        and the meta; every rank packs and copies only its stripe of the image
+        into that one segment; the chunk sums meet on the owner, which
+        publishes the complete meta and only then releases the lock.  The
+        bytes in shm are identical to a single-writer save."""
+        import numpy as np
+        owner = (self._local_rank == self.local_shard_id
+                 and (not self._saving_ranks or self._rank in self._saving_ranks))
+        self.wait_async_save()
+        owner_rank = self._node_ranks[self.local_shard_id]
+        conf.rank = owner_rank
+        conf.group_rank = self._group_rank
+        conf.world_size = self._world_size
+        acquired = self._shm_lock.acquire(blocking=False) if owner else True
+        if not check_all_rank_ready(None, acquired) or not state_dict:
+            logger.info("Rank %s skips saving to memory: the saver is still persisting "
+                        "the previous checkpoint.", self._rank)
+            if owner and acquired:
+                self._shm_lock.release()
+            return False
+        state_dict[DLROVER_CKPT_CONFIG_KEY] = conf
+        index, count = self._node_ranks.index(self._rank), len(self._node_ranks)
+        group = self._node_group
+        try:
+            pending = self._shm_handler.save_state_dict_async(
+                state_dict, stripe=(index, count, owner),
+                attach_barrier=lambda: dist.barrier(group=group))
+        except BaseException:
+            if owner:
+                self._shm_lock.release()
+            raise
+
+        def finish():
+            try:
+                sums = pending.wait_transfer()
+                w0, w1 = pending.window
+                part = (w0, w1, None if sums is None else np.asarray(sums[w0:w1]))
+                parts = [None] * count if owner else None
+                dist.gather_object(part, parts, dst=owner_rank, group=group)
+                if owner:
+                    merged = np.zeros(len(sums), dtype=np.uint32)
+                    for a, b, values in parts:
+                        merged[a:b] = values
+                    pending.publish(merged)
+                else:
+                    pending.abandon(conf.step)
+            finally:
+                if owner:
+                    self._shm_lock.release()
+
+        pending.wait_packed()  # tensors are snapshotted: training may go on
+        self._cached_step = conf.step
+        if self._async_save:
+            self._finisher = threading.Thread(target=finish, name="fcp-finisher", daemon=True)
+            self._finisher.start()
+        else:
+            finish()
+        return True
+
     # -- load ------------------------------------------------------------------
+    def _load_from_peers(self, into, device):
+        """Replicated state on a GPU job: stripes of the image come from the
+        peers' HBM over NVLink, each stripe crossing the host link at most once
+        per node (peer_restore.py).  -> (step, state_dict), or None when that
+        path does not apply and the reference behaviour follows."""
+        from . import peer_restore
+        if not peer_restore.applicable(self, into, device):
+            return None
+        if into is not None and DLROVER_CKPT_CONFIG_KEY not in into:
+            into = dict(into)
+        try:
+            got = peer_restore.restore_replicated(self._shm_handler, into, device)
+        except Exception as e:  # noqa: BLE001
+            from .._native import ChecksumMismatch
+            if not isinstance(e, ChecksumMismatch):
+                raise
+            logger.error("checkpoint in memory is corrupt (%s); falling back to storage", e)
+            self._memory_restore_wrecked_into = into is not None
+            return 0, {}
+        if got is None:
+            return None
+        step, state_dict = got
+        state_dict.pop(DLROVER_CKPT_CONFIG_KEY, None)
+        logger.info("Load checkpoint at step %s from memory (stripes over NVLink).", step)
+        return step, state_dict
+
     def get_state_dict_from_memory(self, into=None, device=None):
         """(step, state_dict) from shm, ({} if shm holds nothing valid or the
         ranks disagree on the step; ENGINE:332-347).  `into` / `device` select
@@ -292,6 +411,9 @@ class CheckpointEngine(metaclass=ABCMeta):
         checksum mismatch counts as "nothing valid"."""
         self.wait_async_save()
         self._memory_restore_wrecked_into = False
+        got = self._load_from_peers(into, device)
+        if got is not None:
+            return got
         self._restore_memory_from_replica()
         state_dict = {}
         config = self._shm_handler.get_checkpoint_config(CheckpointConfig())

@@ -36,14 +36,15 @@ class FullCheckpointEngine(CheckpointEngine):
 
     def __init__(self, checkpoint_dir, storage, local_shard_num=1, global_shard_num=1,
                  comm_backend="", save_timeout=CheckpointConstant.SAVE_TIMEOUT,
-                 replica_count=0, async_save=None):
+                 replica_count=0, async_save=None, stripe_replicas=None):
         if global_shard_num < local_shard_num:
             global_shard_num = local_shard_num
             logger.info("Set global_shard_num to %s.", local_shard_num)
         self._local_shard_num = local_shard_num
         self._global_shard_num = global_shard_num
         super().__init__(checkpoint_dir, storage, comm_backend, save_timeout,
-                         replica_count=replica_count, async_save=async_save)
+                         replica_count=replica_count, async_save=async_save,
+                         stripe_replicas=stripe_replicas)
 
     def get_saving_ranks(self):
         """The first `local_shard_num` local ranks of every node."""

@@ -111,13 +111,22 @@ class HostMapping(object):
     wait for one piece.  Direct mode needs one registration for the kernel's
     alias and pins everything at once."""
 
-    def __init__(self, buf, nbytes, piece_bytes=REGISTER_PIECE_BYTES):
+    def __init__(self, buf, nbytes, piece_bytes=REGISTER_PIECE_BYTES, byte_range=None):
+        """`byte_range` = (lo, hi): pin only the pieces that overlap it (a rank
+        that writes one stripe of a shared image pins that stripe alone)."""
         self.addr = buffer_address(buf)
         self.nbytes = nbytes
         self.piece = piece_bytes
         self._done = []
         self.register_s = 0.0
         self.complete = False
+        lo, hi = byte_range if byte_range is not None else (0, nbytes)
+        step = self.piece if self.piece else max(self.nbytes, 1)
+        self.lo = (lo // step) * step
+        self.hi = min(nbytes, -(-hi // step) * step)
+
+    def covers(self, lo, hi):
+        return self.complete and self.lo <= lo and hi <= self.hi
 
     def register_all(self, pause=0.0, ready=None):
         """`ready(upto)`: called before a piece is pinned; returns once the
@@ -125,7 +134,7 @@ class HostMapping(object):
         being populated in the background, SharedMemory.wait_populated)."""
         t0 = time.time()
         step = self.piece if self.piece else max(self.nbytes, 1)
-        for off in range(0, self.nbytes, step):
+        for off in range(self.lo, self.hi, step):
             if ready is not None:
                 ready(min(off + step, self.nbytes))
             _native.host_register(self.addr + off, min(step, self.nbytes - off))
@@ -172,6 +181,8 @@ class DeviceShardEngine(object):
         self._mapping_job = None  # background registration after a cold restore
         self._keepalive = []
         self._save_bytes = 0
+        self._window = None
+        self._restore_host_leaves = []
         self._warned_host_leaves = False
         self.stats = {}
 
@@ -298,16 +309,18 @@ class DeviceShardEngine(object):
     def _piece_bytes(self):
         return 0 if self.mode == _native.MODE_DIRECT else REGISTER_PIECE_BYTES
 
-    def _ensure_mapping(self, buf, total, ready=None):
+    def _ensure_mapping(self, buf, total, ready=None, byte_range=None):
         self._join_mapping_job()
         addr = buffer_address(buf)
+        lo, hi = byte_range if byte_range is not None else (0, total)
         if self._mapping is not None and (self._mapping.addr != addr
                                           or self._mapping.nbytes < total
-                                          or not self._mapping.complete):
+                                          or not self._mapping.covers(lo, hi)):
             self._mapping.close()
             self._mapping = None
         if self._mapping is None and total:
-            self._mapping = HostMapping(buf, total, self._piece_bytes()).register_all(ready=ready)
+            self._mapping = HostMapping(buf, total, self._piece_bytes(),
+                                        byte_range).register_all(ready=ready)
             self.stats["register_s"] = self._mapping.register_s
         if self._plan is not None:
             self._plan.set_copy_piece_bytes(self._piece_bytes())
@@ -321,18 +334,37 @@ class DeviceShardEngine(object):
             return contextlib.nullcontext()
         return torch.cuda.nvtx.range(name)
 
-    def save_begin(self, leaves, total, buf, ready=None):
+    def stripe_of(self, total, index, count):
+        """(chunk_begin, chunk_end) of stripe `index` when an image of `total`
+        bytes is cut into `count` runs of whole chunks, as equal as possible."""
+        n_chunks = -(-total // self.chunk_bytes)
+        per = -(-n_chunks // count)
+        return min(n_chunks, index * per), min(n_chunks, (index + 1) * per)
+
+    def save_begin(self, leaves, total, buf, ready=None, window=None):
         """Enqueue pack + transfer of the shard into `buf`; returns once the
         work is enqueued.  Call save_packed_wait() before mutating the tensors
         and save_finish() for durability + checksums.  `ready`: see
-        HostMapping.register_all."""
+        HostMapping.register_all.  `window` = (chunk_begin, chunk_end): move
+        only that stripe of the image (a replicated group where every rank
+        writes one stripe over its own host link); staged modes only."""
         with torch.cuda.device(self.device):
             t0 = time.perf_counter()
             with self._nvtx("fcp.plan"):
                 ptrs, offs, sizes, host = self._sources(leaves)
                 plan = self._ensure_plan(ptrs, offs, sizes, total)
+            byte_range = None
+            if window is not None:
+                if self.mode == _native.MODE_DIRECT:
+                    raise ValueError("striped saves need a staged transfer mode")
+                byte_range = (window[0] * self.chunk_bytes,
+                              min(total, window[1] * self.chunk_bytes))
+                plan.set_window(window[0], window[1])
+            else:
+                plan.set_window()
+            self._window = window
             with self._nvtx("fcp.pin"):
-                addr = self._ensure_mapping(buf, total, ready)
+                addr = self._ensure_mapping(buf, total, ready, byte_range)
             stream = torch.cuda.current_stream(self.device)
             with self._nvtx("fcp.host_leaves"):
                 self._stage_host_leaves(host, to_device=True)
@@ -350,7 +382,7 @@ class DeviceShardEngine(object):
                 self.tuner.kernel_leg_failed()
                 self.mode = _native.MODE_STAGED
                 plan.save_async(staging_ptr, addr, self.mode, self.checksum, stream.cuda_stream)
-            self._save_bytes = total
+            self._save_bytes = total if byte_range is None else max(0, byte_range[1] - byte_range[0])
             self.stats["plan_s"] = t1 - t0
 
     def save_packed_wait(self):
@@ -413,7 +445,7 @@ class DeviceShardEngine(object):
             pin_later = False
             t_ready = time.perf_counter()
             cold = (self._mapping is None or self._mapping.addr != buffer_address(buf)
-                    or self._mapping.nbytes < total)
+                    or self._mapping.nbytes < total or not self._mapping.covers(0, total))
             if transient:
                 if total:
                     plan.restore_bounced(buffer_address(buf), staging_ptr, checksum, expected,
@@ -477,6 +509,54 @@ class DeviceShardEngine(object):
             finally:
                 plan.set_read_prefetch(True)
             self._stage_host_leaves(host, to_device=False)
+
+    # -- striped restore of a replicated group ------------------------------
+    def prepare_restore(self, leaves, total):
+        """Plan + staging for a restore whose bytes arrive in pieces
+        (stage_range / restore_from_slices).  Returns the staging tensor."""
+        with torch.cuda.device(self.device):
+            for lf in leaves:
+                if lf.is_cuda and lf.nbytes and not lf.tensor.is_contiguous():
+                    raise ValueError("restore target must be contiguous")
+            ptrs, offs, sizes, host = self._sources(leaves)
+            plan = self._ensure_plan(ptrs, offs, sizes, total)
+            plan.set_window()
+            if total and self._staging is None:
+                self._staging = torch.empty(plan.staging_bytes, dtype=torch.uint8,
+                                            device=self.device)
+            self._restore_host_leaves = host
+            return self._staging
+
+    def stage_range(self, buf, total, lo, hi):
+        """Host image bytes [lo, hi) -> the same offsets of the HBM staging
+        (copy engine if the segment is pinned there, pinned ring otherwise)."""
+        with torch.cuda.device(self.device):
+            self._join_mapping_job()
+            addr = buffer_address(buf)
+            pinned = (self._mapping is not None and self._mapping.addr == addr
+                      and self._mapping.covers(lo, hi))
+            if pinned:
+                self._plan.set_copy_piece_bytes(self._piece_bytes())
+            stream = torch.cuda.current_stream(self.device)
+            self._plan.stage_range(addr, self._staging.data_ptr(), lo, hi, registered=pinned,
+                                   n_workers=int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
+                                   stream=stream.cuda_stream)
+            self.stats["stage_path"] = "registered" if pinned else "bounced"
+            self.stats["stage_ms"] = self._plan.timings()["total_ms"]
+
+    def restore_from_slices(self, total, bases, slice_bytes, expected=None, local=False):
+        """One scatter launch over an image whose slice s is read through
+        bases[s] (own staging or peers' staging mapped with CUDA IPC); call
+        prepare_restore first.  `local`: every base is this GPU's memory."""
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream(self.device)
+            checksum = self.checksum if expected is not None else _native.SUM_NONE
+            self._plan.restore_from_slices(bases, slice_bytes, checksum, expected,
+                                           read_prefetch=local, stream=stream.cuda_stream)
+            self._stage_host_leaves(self._restore_host_leaves, to_device=False)
+            self._restore_host_leaves = []
+            self.stats.update(self._plan.timings())
+            self.stats["restore_path"] = "slices_local" if local else "slices_nvlink"
 
     @property
     def staging(self):

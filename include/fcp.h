@@ -249,6 +249,45 @@ int fcp_restore_bounced(fcp_plan* plan, const void* host_src, void* staging,
 int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
                             const uint32_t* expected, void* stream);
 
+/* The same for an image whose pieces sit in SEVERAL device buffers — the HBM
+ * staging of the ranks of a replicated (DDP) group, mapped here with
+ * fcp_ipc_open — so that a restore crosses the host link once per node
+ * instead of once per rank (the reference has every local rank read the whole
+ * image from shard 0's shm, full_ckpt_engine.py:145-166, and moves replica
+ * bytes through gloo on CPU tensors, REPL:275-332).  Slice s = image bytes
+ * [s*slice_bytes, (s+1)*slice_bytes) is read through slice_bases[s], which is
+ * the address image byte 0 WOULD have in that buffer (absolute offsets apply;
+ * the buffer only needs to hold the slices that name it: no region reads
+ * outside itself).  slice_bytes: a multiple of FCP_REGION_BYTES.  One scatter
+ * launch pulls every slice over NVLink with plain per-thread loads, verifies
+ * the CRC-32C of every chunk and unpacks into the live tensors; pass
+ * read_prefetch = 0 when any base is peer memory (see
+ * fcp_plan_set_read_prefetch).  Synchronous.                                */
+int fcp_restore_from_slices(fcp_plan* plan, const void* const* slice_bases,
+                            uint64_t n_slices, uint64_t slice_bytes,
+                            int checksum, const uint32_t* expected,
+                            int read_prefetch, void* stream);
+
+/* Host -> staging copy of image bytes [byte_begin, byte_end) only, no
+ * kernel: the host-link leg of a striped restore, where every rank of a
+ * replicated group fetches 1/n of the shm image (then see
+ * fcp_restore_from_slices).  registered != 0: `host_src` is pinned
+ * (fcp_host_register), plain copy-engine transfer; else the bytes go through
+ * the plan's pinned ring with `n_workers` host threads as in
+ * fcp_restore_bounced.  Synchronous.                                        */
+int fcp_stage_range(fcp_plan* plan, const void* host_src, void* staging,
+                    uint64_t byte_begin, uint64_t byte_end, int registered,
+                    int n_workers, void* stream);
+
+/* Restrict the following fcp_save_async calls of this plan to chunks
+ * [chunk_begin, chunk_end): only those are packed, checksummed and copied to
+ * the host image (staged modes).  A replicated group saves ONE image with
+ * every rank writing its own stripe of it over its own host link (the
+ * reference lets local rank 0 write all of it, full_ckpt_engine.py:75-88).
+ * fcp_save_wait still fills one value per chunk of the image; only those of
+ * the window are meaningful.  (0, UINT64_MAX) = everything (default).       */
+int fcp_plan_set_window(fcp_plan* plan, uint64_t chunk_begin, uint64_t chunk_end);
+
 /* Let kernels running on `device` dereference memory of `peer` (NVLink /
  * NVSwitch P2P).  With it, fcp_restore_from_device can be given a pointer to
  * the SURVIVING rank's staging image (mapped into this process with CUDA

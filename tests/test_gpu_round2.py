@@ -134,3 +134,97 @@ def test_host_crc_matches_recorded_sums_of_a_save():
     assert got.tolist() == sums.tolist()
     assert got.tolist() == oracle.chunk_crc32c_fast(host.numpy(), _native.DEFAULT_CHUNK_BYTES).tolist()
     plan.close()
+
+
+# ------------------------------------------------ stripes and sliced scatter
+def _random_case(seed, n_tensors, max_bytes, dev):
+    rng = np.random.default_rng(seed)
+    tensors, offs, sizes, off = [], [], [], 0
+    for _ in range(n_tensors):
+        k = int(rng.integers(1, max_bytes))
+        tensors.append(torch.from_numpy(rng.integers(0, 256, k, dtype=np.uint8)).to(dev))
+        off += int(rng.integers(0, 6))  # holes + misalignment
+        offs.append(off)
+        sizes.append(k)
+        off += k
+    return tensors, offs, sizes, off
+
+
+def _oracle_image(tensors, offs, sizes, total):
+    host = [t.cpu().numpy() for t in tensors]
+    d = np.zeros(len(host), dtype=oracle.DESC_DTYPE)
+    d["ptr"] = [h.ctypes.data for h in host]
+    d["dst_off"], d["nbytes"] = offs, sizes
+    return oracle.pack_descs(d, total)
+
+
+@pytest.mark.parametrize("n_writers", [2, 3, 8])
+def test_striped_save_equals_single_writer_image(n_writers):
+    """n plans over the SAME tensors (the ranks of a replicated group), each
+    restricted to its chunk window, write one host image: bytes and merged sums
+    equal the oracle's."""
+    dev = torch.device("cuda", 0)
+    tensors, offs, sizes, total = _random_case(40 + n_writers, 60, 900000, dev)
+    image = _oracle_image(tensors, offs, sizes, total)
+    want_sums = oracle.chunk_crc32c(image, CHUNK)
+    n_chunks = len(want_sums)
+    per = -(-n_chunks // n_writers)
+    host = torch.full((total,), 0x77, dtype=torch.uint8).pin_memory()
+    merged = np.zeros(n_chunks, dtype=np.uint32)
+    stream = torch.cuda.current_stream().cuda_stream
+    plans = []
+    for w in range(n_writers):
+        plan = _native.Plan(_native.make_descs([t.data_ptr() for t in tensors], offs, sizes),
+                            total, 0, CHUNK)
+        staging = torch.full((plan.staging_bytes,), 0xEE, dtype=torch.uint8, device=dev)
+        w0, w1 = min(n_chunks, w * per), min(n_chunks, (w + 1) * per)
+        plan.set_window(w0, w1)
+        plan.save_async(staging.data_ptr(), host.data_ptr(), _native.MODE_STAGED,
+                        _native.SUM_CRC32C, stream)
+        sums = plan.save_wait()
+        merged[w0:w1] = sums[w0:w1]
+        # nothing outside the window moved
+        if w0 > 0:
+            assert int(staging[0]) == 0xEE
+        plans.append((plan, staging, w0, w1))
+    assert host.numpy().tobytes() == image.tobytes()
+    assert merged.tolist() == want_sums.tolist()
+    # --- sliced scatter: slice s is read from writer s's staging (each holds
+    # only its own stripe), one launch, all sums verified
+    fresh = [torch.zeros_like(t) for t in tensors]
+    reader = _native.Plan(_native.make_descs([t.data_ptr() for t in fresh], offs, sizes),
+                          total, 0, CHUNK)
+    bases = [st.data_ptr() for _, st, _, _ in plans]
+    reader.restore_from_slices(bases, per * CHUNK, _native.SUM_CRC32C, expected=want_sums,
+                               read_prefetch=True, stream=stream)
+    for a, b in zip(tensors, fresh):
+        assert torch.equal(a, b)
+    # a wrong byte in one provider's stripe is caught
+    _, st1, w0, _ = plans[1]
+    st1[w0 * CHUNK + 5] ^= 1
+    with pytest.raises(_native.ChecksumMismatch):
+        reader.restore_from_slices(bases, per * CHUNK, _native.SUM_CRC32C, expected=want_sums,
+                                   read_prefetch=False, stream=stream)
+    for plan, _, _, _ in plans:
+        plan.close()
+    reader.close()
+
+
+@pytest.mark.parametrize("registered", [False, True])
+def test_stage_range_moves_exactly_the_range(registered):
+    dev = torch.device("cuda", 0)
+    total = (9 << 20) + 12345
+    rng = np.random.default_rng(9)
+    src = torch.from_numpy(rng.integers(0, 256, total, dtype=np.uint8))
+    if registered:
+        src = src.pin_memory()
+    t = torch.zeros(total, dtype=torch.uint8, device=dev)
+    plan = _native.Plan(_native.make_descs([t.data_ptr()], [0], [total]), total, 0, CHUNK)
+    staging = torch.full((plan.staging_bytes,), 0xC3, dtype=torch.uint8, device=dev)
+    lo, hi = 3 * CHUNK, 3 * CHUNK + (5 << 20) + 77
+    plan.stage_range(src.data_ptr(), staging.data_ptr(), lo, hi, registered=registered,
+                     stream=torch.cuda.current_stream().cuda_stream)
+    got = staging.cpu().numpy()
+    assert got[lo:hi].tobytes() == src.numpy()[lo:hi].tobytes()
+    assert (got[:lo] == 0xC3).all() and (got[hi:total] == 0xC3).all()
+    plan.close()

@@ -194,3 +194,35 @@ def test_raw_file_records_sums_of_its_own_payload(monkeypatch):
         finally:
             h.close()
             h.unlink()
+
+
+# ------------------------------------------------ peer restore: who provides
+def test_plan_providers():
+    from dlrover_wuqiong_b200.flash_checkpoint.peer_restore import plan_providers
+    MB = 1 << 20
+    total, chunk = 10 * MB + 5, 2 * MB  # 6 chunks
+
+    def f(host, hbm=(0, 0, 0), shm=0):
+        return {"host": host, "hbm": hbm, "shm_step": shm}
+
+    # restart: nobody holds HBM, every rank stages its stripe from shm
+    got = plan_providers([f("a", shm=5), f("a", shm=5), f("a", shm=5)], 5, total, chunk)
+    assert got == {"a": [(0, 4 * MB, 0, True), (4 * MB, 8 * MB, 1, True),
+                         (8 * MB, total, 2, True)]}
+    # one survivor holds the whole image: it provides every stripe the others lack
+    got = plan_providers([f("a", hbm=(5, 0, total), shm=5), f("a")], 5, total, chunk)
+    assert got == {"a": [(0, 6 * MB, 0, False), (6 * MB, total, 0, False)]}
+    # striped save, then rank 1 was replaced: it re-stages its own stripe from shm
+    got = plan_providers([f("a", hbm=(5, 0, 6 * MB), shm=5), f("a", shm=5)], 5, total, chunk)
+    assert got == {"a": [(0, 6 * MB, 0, False), (6 * MB, total, 1, True)]}
+    # a stale HBM image (older step) does not count
+    got = plan_providers([f("a", hbm=(4, 0, total), shm=5), f("a", shm=5)], 5, total, chunk)
+    assert got["a"][0][3] is True and got["a"][1][3] is True
+    # a host with neither HBM nor shm for a stripe: not handled
+    assert plan_providers([f("a", hbm=(5, 0, total)), f("b")], 5, total, chunk) is None
+    # two hosts, each stripes its own shm; more ranks than chunks leaves empty stripes
+    got = plan_providers([f("a", shm=5), f("b", shm=5)], 5, 100, chunk)
+    assert got == {"a": [(0, 100, 0, True)], "b": [(0, 100, 1, True)]}
+    got = plan_providers([f("a", shm=5)] * 4, 5, 3 * MB, chunk)
+    assert [s[:2] for s in got["a"]] == [(0, 2 * MB), (2 * MB, 3 * MB), (3 * MB, 3 * MB),
+                                         (3 * MB, 3 * MB)]
