@@ -100,9 +100,15 @@ _COMPACT_TAG = "\0fcp_t"
 def _compact(value):
     """Non-sharded tensors travel in every rank's meta dict (broadcast from
     rank 0, then pickled to the agent) on every save; a tensor pickles ~100x
-    slower than its bytes, so they go as (tag, dtype name, shape, bytes)."""
+    slower than its bytes, so they go as (tag, dtype name, shape, bytes).
+    This is a deviation from the reference's meta (which holds the tensors
+    themselves, FSDPE:98-102): a reader written against the reference would
+    not understand the tuples.  FCP_DCP_COMPACT=0 keeps the reference's
+    encoding (this package's reader accepts both)."""
     if torch.is_tensor(value):
         t = value.detach().cpu().contiguous()
+        if os.getenv("FCP_DCP_COMPACT", "1") != "1":
+            return t
         return (_COMPACT_TAG, str(t.dtype).split(".", 1)[1], tuple(t.shape),
                 t.reshape(-1).view(torch.uint8).numpy().tobytes())
     return value
