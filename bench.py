@@ -644,6 +644,8 @@ def leg_megatron(device, ckpt_root):
             os.environ.pop("FCP_RESTORE_DEVICE", None)
             assert it == 12 and _digest(sd, device) == want, "megatron restore differs"
             if env is None:
+                out["load_breakdown"] = {k: handler.last_stats.get(k) for k in (
+                    "restore_prepare_s", "restore_move_s", "restore_host_leaves_s")}
                 out["restore_path"] = handler.last_stats.get("restore_path")
                 out["framework_got_tensors_on"] = seen["devices"]
                 assert out["restore_path"] in ("registered", "bounced"), out["restore_path"]
@@ -744,8 +746,8 @@ def leg_fsdp(device, rank, world, ckpt_root, saves=4):
 
     def live_tensors():
         out = [p for p in model.parameters()]
-        for st in opt.state.values():
-            out += [v for v in st.values() if torch.is_tensor(v)]
+        for st in opt.state.values():  # by key: load_state_dict may reorder a state's entries
+            out += [st[k] for k in sorted(st) if torch.is_tensor(st[k])]
         return out
 
     train_step()
@@ -796,8 +798,16 @@ def leg_fsdp(device, rank, world, ckpt_root, saves=4):
     finally:
         fsdp_engine.SharedMemoryReader.read_data = real
     assert extra["step"] == saves, extra
-    for a, b in zip(snap, live_tensors()):
-        assert torch.equal(a, b.detach()), "fsdp restore differs"
+    n_params = sum(1 for _ in model.parameters())
+    now = live_tensors()
+    assert len(now) == len(snap), "fsdp restore: %d tensors before, %d after" % (len(snap), len(now))
+    for i, (a, b) in enumerate(zip(snap, now)):
+        if not torch.equal(a, b.detach()):
+            bad = (a != b.detach()).reshape(-1).nonzero()
+            raise AssertionError(
+                "fsdp restore differs: tensor %d (%s, shape %s, %s): %d of %d elements, first at %d"
+                % (i, "parameter" if i < n_params else "optimizer state", tuple(a.shape), a.dtype,
+                   bad.numel(), a.numel(), int(bad[0]) if bad.numel() else -1))
     restore_path = handler.last_stats.get("restore_path")
     assert restore_path in ("registered", "bounced"), restore_path
     n_items = len(handler.metadata.get(local=True)["dcp_metadata"].storage_data)

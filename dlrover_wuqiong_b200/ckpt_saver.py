@@ -241,6 +241,7 @@ class SharedMemoryHandler(object):
         # what the engine's HBM staging holds: (step, byte_lo, byte_hi) of a
         # complete, checksummed image (or stripe of one); step 0 = nothing
         self._staged = (0, 0, 0)
+        self._view_alias = None
 
     # -- lifecycle ----------------------------------------------------------
     def _note_staged(self, step, window=None):
@@ -295,6 +296,7 @@ class SharedMemoryHandler(object):
 
     def init_shared_memory(self, create=False, size=0):
         self._drop_engine()
+        self._view_alias = None  # (unmapped once the views over it are gone)
         self.shared_memory = _create_shared_memory(self._shm_name, create=create, size=size)
         self._need_creation = False
 
@@ -468,7 +470,8 @@ class SharedMemoryHandler(object):
         ``into``: a state dict of the same structure whose tensors receive the
         bytes in place (CUDA tensors through the scatter kernel).  ``device``:
         allocate fresh tensors there instead (leaves that were host-resident
-        at save time stay on the host).  Given both, `into` may cover only
+        at save time stay on the host; the device tensors are views of one
+        allocation, so keeping any of them keeps all of it).  Given both, `into` may cover only
         part of the structure (say, the optimizer shards) and the rest is
         allocated on `device`.  All variants verify the CRC-32C recorded at
         save time.  Returns {} when the shm holds no complete checkpoint."""
@@ -481,8 +484,27 @@ class SharedMemoryHandler(object):
         if not self.shared_memory:
             return {}
         if into is None and device is None:
-            return _read_state_dict_from_shm(_strip_private(meta_dict), self.shared_memory)
+            return _read_state_dict_from_shm(_strip_private(meta_dict), self._view_source())
         return self._load_into(meta_dict, into, device)
+
+    def _view_source(self):
+        """What the zero-copy CPU views of load_state_dict() alias.  In a
+        process whose engine pinned the segment piece by piece, views over
+        that mapping look like pinned memory to CUDA, and a later
+        ``cuda_tensor.copy_(view)`` of a tensor that straddles two pieces is
+        rejected (a transfer may not span two registrations).  Such a process
+        hands out views over a second, unregistered mapping of the same
+        segment: plain pageable memory, exactly what the reference's views
+        are."""
+        if self._engine is None or getattr(self.shared_memory, "_fd", -1) < 0:
+            return self.shared_memory
+        alias = self._view_alias
+        if alias is None or alias.size != self.shared_memory.size:
+            import mmap
+            alias = _ShmAlias(mmap.mmap(self.shared_memory._fd, self.shared_memory.size,
+                                        flags=mmap.MAP_SHARED))
+            self._view_alias = alias
+        return alias
 
     def load_raw_images(self):
         """{state name: RawImage} over the shm, for the saver's raw persist
@@ -502,19 +524,11 @@ class SharedMemoryHandler(object):
     def _load_into(self, meta_dict, into, device):
         total = self.shared_memory.size
         public = _strip_private(meta_dict)
-        dev = torch.device(device) if device is not None else None
         # leaves that lived in host memory when the image was packed (rng
         # states, a CPU `step`) come back as host tensors: their consumers
         # (torch.set_rng_state ...) want them there
-        host_idx = set((meta_dict.get(FCP_CHECKSUM_KEY) or {}).get("host_leaves") or ())
-
-        def alloc(index, m):
-            if dev is None:
-                raise ValueError("`into` does not match the structure of the checkpoint "
-                                 "in memory (pass device= to allocate what it lacks)")
-            where = "cpu" if index in host_idx else dev
-            return torch.empty(m.shape, dtype=m.dtype, device=where)
-
+        host_idx = (meta_dict.get(FCP_CHECKSUM_KEY) or {}).get("host_leaves") or ()
+        alloc = _plan.arena_allocator(device, host_idx)
         leaves = _plan.pair_or_alloc(public, into, alloc)
         engine = self._engine_for(leaves)
         if engine is not None:
@@ -667,6 +681,16 @@ class SharedMemoryHandler(object):
     def get_checkpoint_config(self, default_config):
         meta_dict = self.metadata.get_keys([DLROVER_CKPT_CONFIG_KEY])
         return meta_dict.get(DLROVER_CKPT_CONFIG_KEY, default_config)
+
+
+class _ShmAlias(object):
+    """A second mapping of a segment; quacks like SharedMemory for the view
+    builders (``.buf``)."""
+
+    def __init__(self, mm):
+        self._mmap = mm
+        self.buf = memoryview(mm)
+        self.size = len(mm)
 
 
 def _strip_private(meta_dict):

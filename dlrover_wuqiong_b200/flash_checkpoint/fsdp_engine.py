@@ -420,6 +420,7 @@ class SharedMemoryReader(StorageReader):
                 from ..transfer import checksums_from_meta
                 expected = checksums_from_meta(self._checksums, total, engine.chunk_bytes)
             engine.restore(leaves, total, h.shared_memory.buf, expected)
+            h.last_stats = dict(engine.stats)
             self._verified = self._verified or expected is not None
             for item, target, recv, whole, _ in device_jobs:
                 if not whole:

@@ -172,15 +172,7 @@ def restore_replicated(handler, into, device, group=None):
 
     # ---- 3. leaves, plan, staging
     public = _strip_private(meta)
-    target = torch.device(device) if device is not None else None
-    host_idx = set(entry.get("host_leaves") or ())
-
-    def alloc(index, m):
-        if target is None:
-            raise ValueError("`into` does not match the structure of the checkpoint in "
-                             "memory (pass device= to allocate what it lacks)")
-        return torch.empty(m.shape, dtype=m.dtype,
-                           device="cpu" if index in host_idx else target)
+    alloc = _plan.arena_allocator(device, entry.get("host_leaves") or ())
 
     error = None
     staging = None

@@ -134,14 +134,15 @@ def count_tensor_metas(meta_tree):
     return n
 
 
-def pair_or_alloc(meta_tree, into, alloc):
+def pair_or_alloc(meta_tree, into, alloc_many):
     """Leaves for a restore: walk `meta_tree`; where `into` (a possibly
     partial mirror of the tree, or None) holds a tensor at the same place it
-    receives the bytes, elsewhere ``alloc(index, meta)`` supplies a fresh
-    tensor (`index` = position of the leaf in layout order).  A tensor in
-    `into` whose dtype or element count differs from the checkpoint's raises
-    ValueError.  Returns the leaf list in layout order."""
-    leaves = []
+    receives the bytes; all the others are supplied by ONE call
+    ``alloc_many([(index, meta), ...]) -> [tensor, ...]`` (`index` = position
+    of the leaf in layout order).  A tensor in `into` whose dtype or element
+    count differs from the checkpoint's raises ValueError.  Returns the leaf
+    list in layout order."""
+    slots = []  # [meta, tensor or None]
     missing = object()
 
     def child(container, key):
@@ -167,10 +168,43 @@ def pair_or_alloc(meta_tree, into, alloc):
                         "`into` does not match the checkpoint at %s: %s%s there, %s%s here"
                         % ("/".join(map(str, path)), m.dtype, tuple(m.shape), v.dtype,
                            tuple(v.shape)))
-                t = v
+                slots.append([m, v])
             else:
-                t = alloc(len(leaves), m)
-            leaves.append(Leaf(t, m))
+                slots.append([m, None])
 
     walk(meta_tree, into if into is not None else missing, ())
-    return leaves
+    wanted = [(i, m) for i, (m, t) in enumerate(slots) if t is None]
+    if wanted:
+        for (i, _), t in zip(wanted, alloc_many(wanted)):
+            slots[i][1] = t
+    return [Leaf(t, m) for m, t in slots]
+
+
+def arena_allocator(device, host_indices=()):
+    """alloc_many for pair_or_alloc: every device leaf is carved out of ONE
+    allocation (a restore of a few thousand tensors otherwise pays a
+    cudaMalloc per large tensor: ~1.3 s for 22 GB in 2400 tensors, measured),
+    256-byte aligned; leaves listed in `host_indices` are host tensors.
+    device None: nothing may be missing."""
+    host_indices = set(host_indices)
+
+    def alloc_many(wanted):
+        if device is None:
+            raise ValueError("`into` does not match the structure of the checkpoint in "
+                             "memory (pass device= to allocate what it lacks)")
+        dev = torch.device(device)
+        on_dev = [(i, m) for i, m in wanted if i not in host_indices and dev.type != "cpu"]
+        need = sum(-(-(m.numel * m.element_size) // 256) * 256 for _, m in on_dev)
+        arena = torch.empty(need, dtype=torch.uint8, device=dev) if need else None
+        out, cursor = {}, 0
+        for i, m in on_dev:
+            n = m.numel * m.element_size
+            if n:
+                out[i] = arena[cursor:cursor + n].view(m.dtype).reshape(m.shape)
+                cursor += -(-n // 256) * 256
+            else:
+                out[i] = torch.empty(m.shape, dtype=m.dtype, device=dev)
+        return [out[i] if i in out else torch.empty(m.shape, dtype=m.dtype)
+                for i, m in wanted]
+
+    return alloc_many

@@ -287,3 +287,28 @@ def test_partial_into_allocates_the_rest_on_the_device(saver_env):
         with pytest.raises(ValueError):  # wrong size where `into` does name a leaf
             ckpt.load_checkpoint(into={"optim": {"m": torch.zeros(5, device=dev)}}, device=dev)
         ckpt.close()
+
+
+def test_cpu_views_of_a_pinned_segment_copy_to_the_gpu(saver_env):
+    """The reference's restore: load_checkpoint() returns CPU views and the
+    user copies them up per tensor.  In the process that saved, the segment is
+    pinned in 64 MiB pieces; a view that straddles two pieces must still be
+    an ordinary (pageable) source for cuda_tensor.copy_()."""
+    from dlrover_wuqiong_b200.flash_checkpoint.ddp import DdpCheckpointer
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(8)
+    sd = {"small": torch.randn(1000, device=dev),
+          "big": torch.randn(48 << 20, device=dev),     # 192 MiB: spans several pieces
+          "tail": torch.randn(12345, device=dev)}
+    with tempfile.TemporaryDirectory() as tmpdir:
+        ckpt = DdpCheckpointer(tmpdir)
+        assert ckpt.save_checkpoint(1, sd, storage_type=StorageType.MEMORY)
+        views = ckpt.load_checkpoint()
+        assert not views["big"].is_cuda
+        for k, v in sd.items():
+            up = torch.empty_like(v)
+            up.copy_(views[k])
+            torch.cuda.synchronize()
+            assert torch.equal(up, v), k
+        del views
+        ckpt.close()
