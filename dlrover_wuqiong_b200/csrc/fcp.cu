@@ -82,6 +82,12 @@ int init_device(int dev) {
   fcpcrc::make_table(fcpcrc::shift_bytes(fcpk::kRegion), &tab[fcpk::kTabF]);
   FCP_CUDA(cudaMemcpyToSymbol(fcpk::g_fcp_tab, tab.data(),
                               sizeof(uint32_t) * fcpk::kTabWords));
+  std::vector<uint32_t> reg(fcpk::kRegionShiftTabs * 1024);
+  for (int j = 0; j < fcpk::kRegionShiftTabs; ++j)
+    fcpcrc::make_table(fcpcrc::shift_bytes(static_cast<uint64_t>(fcpk::kRegion) << j),
+                       &reg[j * 1024]);
+  FCP_CUDA(cudaMemcpyToSymbol(fcpk::g_fcp_tab_regions, reg.data(),
+                              sizeof(uint32_t) * reg.size()));
   int sms = 0;
   FCP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   g_sm_count[dev] = sms;
@@ -167,8 +173,8 @@ int launch_finalize(const uint32_t* region_sums, uint32_t* chunk_sums,
                     uint64_t chunk_begin, uint64_t chunk_end, cudaStream_t st) {
   const uint64_t nc = chunk_end - chunk_begin;
   if (nc == 0) return 0;
-  const unsigned threads = 64;
-  const unsigned grid = static_cast<unsigned>(ceil_div(nc, threads));
+  const unsigned threads = 128;  // one warp per chunk
+  const unsigned grid = static_cast<unsigned>(ceil_div(nc, threads / 32));
   fcpk::fcp_finalize_kernel<<<grid, threads, 0, st>>>(
       region_sums, chunk_sums, n_regions, regions_per_chunk, chunk_begin,
       chunk_end);

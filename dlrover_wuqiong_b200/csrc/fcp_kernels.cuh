@@ -35,9 +35,13 @@ constexpr int kTabK = 1024;         // shift 992 B (row stride - word)
 constexpr int kTabC = 2048;         // 5 tables: shift 32,64,128,256,512 B
 constexpr int kTabF = 2048 + 5120;  // shift one region (16 KiB)
 constexpr int kTabWords = kTabF + 1024;
+// shift by 2^j regions, j = 0 .. kRegionShiftTabs-1 (chunk_bytes is a uint32:
+// at most 2^18 regions per chunk); used by the chunk finaliser
+constexpr int kRegionShiftTabs = 19;
 
 // per-device constant tables, filled once by fcp_init()
-static __device__ uint32_t g_fcp_tab[kTabWords];
+static __device__ __align__(16) uint32_t g_fcp_tab[kTabWords];
+static __device__ __align__(16) uint32_t g_fcp_tab_regions[kRegionShiftTabs * 1024];
 
 struct W8 {
   uint32_t v[8];

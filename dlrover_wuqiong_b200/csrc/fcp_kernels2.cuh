@@ -15,41 +15,64 @@ namespace fcpk {
 // ---- word-level slow paths (tensor boundaries, gaps, tail of the image) ----
 
 // PACK: assemble the 32 packed bytes [o, o+32) from whatever descriptors
-// cover them; uncovered / out-of-range bytes are zero.
+// cover them; uncovered / out-of-range bytes are zero.  One pass per
+// descriptor that overlaps the word (typically two at a tensor boundary):
+// its bytes are fetched with predicated byte loads at compile-time positions,
+// so the word stays in registers and the loads go out back to back.
 __device__ __noinline__ W8 gather_word(Cur& c, const fcp_desc* __restrict__ d,
                                        uint32_t n, uint64_t o, uint64_t total) {
   W8 w;
 #pragma unroll
   for (int i = 0; i < 8; ++i) w.v[i] = 0u;
+  const uint64_t end = o + kWordBytes < total ? o + kWordBytes : total;
+  uint64_t p = o;
+  while (p < end) {
+    cur_seek(c, d, n, p);          // first descriptor that ends beyond p
+    if (c.off >= end) break;       // nothing but a gap up to the end of the word
+    const uint32_t a = static_cast<uint32_t>((c.off > p ? c.off : p) - o);
+    const uint32_t b = static_cast<uint32_t>((c.end < end ? c.end : end) - o);
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(c.ptr + (o - c.off));  // byte i at src[i]
 #pragma unroll
-  for (int b = 0; b < kWordBytes; ++b) {
-    const uint64_t p = o + b;
-    if (p < total) {
-      cur_seek(c, d, n, p);
-      if (c.off <= p) {
-        const uint32_t v = *reinterpret_cast<const uint8_t*>(c.ptr + (p - c.off));
-        w.v[b >> 2] |= v << ((b & 3) * 8);
-      }
-    }
+    for (int i = 0; i < kWordBytes; ++i)
+      if (static_cast<uint32_t>(i) >= a && static_cast<uint32_t>(i) < b)
+        w.v[i >> 2] |= static_cast<uint32_t>(src[i]) << ((i & 3) * 8);
+    p = o + b;
   }
   return w;
 }
 
 // SCATTER: hand the 32 packed bytes [o, o+32) to whatever descriptors cover
-// them, byte by byte.
-__device__ __noinline__ void scatter_word(Cur& c, const fcp_desc* __restrict__ d,
-                                          uint32_t n, uint64_t o, uint64_t total,
-                                          const W8& w) {
+// them; same structure as gather_word.  The word comes as scalars (a
+// reference parameter would pin the caller's W8 in local memory).
+__device__ __noinline__ void scatter_word_regs(Cur& c, const fcp_desc* __restrict__ d,
+                                               uint32_t n, uint64_t o, uint64_t total,
+                                               uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3,
+                                               uint32_t w4, uint32_t w5, uint32_t w6, uint32_t w7) {
+  const uint64_t end = o + kWordBytes < total ? o + kWordBytes : total;
+  uint64_t p = o;
+  while (p < end) {
+    cur_seek(c, d, n, p);
+    if (c.off >= end) break;
+    const uint32_t a = static_cast<uint32_t>((c.off > p ? c.off : p) - o);
+    const uint32_t b = static_cast<uint32_t>((c.end < end ? c.end : end) - o);
+    uint8_t* dst = reinterpret_cast<uint8_t*>(c.ptr + (o - c.off));
 #pragma unroll
-  for (int b = 0; b < kWordBytes; ++b) {
-    const uint64_t p = o + b;
-    if (p < total) {
-      cur_seek(c, d, n, p);
-      if (c.off <= p)
-        *reinterpret_cast<uint8_t*>(c.ptr + (p - c.off)) =
-            static_cast<uint8_t>(w.v[b >> 2] >> ((b & 3) * 8));
+    for (int i = 0; i < kWordBytes; ++i) {
+      const uint32_t w = (i >> 2) == 0 ? w0 : (i >> 2) == 1 ? w1 : (i >> 2) == 2 ? w2
+                       : (i >> 2) == 3 ? w3 : (i >> 2) == 4 ? w4 : (i >> 2) == 5 ? w5
+                       : (i >> 2) == 6 ? w6 : w7;
+      if (static_cast<uint32_t>(i) >= a && static_cast<uint32_t>(i) < b)
+        dst[i] = static_cast<uint8_t>(w >> ((i & 3) * 8));
     }
+    p = o + b;
   }
+}
+
+__device__ __forceinline__ void scatter_word(Cur& c, const fcp_desc* __restrict__ d,
+                                             uint32_t n, uint64_t o, uint64_t total,
+                                             const W8& w) {
+  scatter_word_regs(c, d, n, o, total, w.v[0], w.v[1], w.v[2], w.v[3], w.v[4], w.v[5], w.v[6],
+                    w.v[7]);
 }
 
 // store a packed word whose tail may stick out of the image (PACK side)
@@ -125,11 +148,32 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   uint32_t* sK = sT + 1024 * REPL;  // 1024 * RK words
   uint32_t* sC = sK + 1024 * RK;    // 5120 words
   if (CRC) {
-    for (int i = threadIdx.x; i < 1024 * REPL; i += THREADS)
-      sT[i] = g_fcp_tab[kTabT + i / REPL];
-    for (int i = threadIdx.x; i < 1024 * RK; i += THREADS)
-      sK[i] = g_fcp_tab[kTabK + i / RK];
-    for (int i = threadIdx.x; i < 5120; i += THREADS) sC[i] = g_fcp_tab[kTabC + i];
+    if (REPL == 1) {
+      // unreplicated tables sit in shared memory in the order of the device
+      // blob: one straight copy, all of a thread's 16-byte loads in flight at
+      // once (a dependent word-by-word fill cost ~22 us per CTA on a cold L2,
+      // most of the time of a small image)
+      constexpr int kVec = (1024 + 1024 + 5120) / 4;
+      constexpr int kPer = (kVec + THREADS - 1) / THREADS;
+      const uint4* src = reinterpret_cast<const uint4*>(g_fcp_tab);
+      uint4 tmp[kPer];
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        const int i = threadIdx.x + k * THREADS;
+        if (i < kVec) tmp[k] = __ldg(src + i);
+      }
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        const int i = threadIdx.x + k * THREADS;
+        if (i < kVec) reinterpret_cast<uint4*>(smem)[i] = tmp[k];
+      }
+    } else {
+      for (int i = threadIdx.x; i < 1024 * REPL; i += THREADS)
+        sT[i] = g_fcp_tab[kTabT + i / REPL];
+      for (int i = threadIdx.x; i < 1024 * RK; i += THREADS)
+        sK[i] = g_fcp_tab[kTabK + i / RK];
+      for (int i = threadIdx.x; i < 5120; i += THREADS) sC[i] = g_fcp_tab[kTabC + i];
+    }
     __syncthreads();
   }
   const int lane = threadIdx.x & 31;
@@ -281,7 +325,10 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
         }
       }
     } else {
-      // General path: every word decides for itself.
+      // General path: every word decides for itself.  (Keeping several rows
+      // in flight here was tried for images of many small tensors: no gain
+      // with a warm L2 — such images are bound by the two dependent launches,
+      // ~24 us on the GPU, and by the host's ~30 us to enqueue a call.)
 #pragma unroll 1
       for (int row = 0; row < kRows; ++row) {
         const uint64_t o = lane_o + static_cast<uint64_t>(row) * kRowBytes;
@@ -439,35 +486,57 @@ __global__ void __launch_bounds__(128) fcp_xxh64_kernel(const uint8_t* __restric
   out[chunk] = h;
 }
 
-// One thread per chunk: Horner over the chunk's region values.  The value
-// written is the raw CRC of the chunk zero-padded to a whole number of
-// regions; the host strips the padding and applies init/xorout
-// (fcp_finish_checksums).
-__global__ void fcp_finalize_kernel(const uint32_t* __restrict__ region_sums,
-                                    uint32_t* __restrict__ chunk_sums,
-                                    uint64_t n_regions,
-                                    uint32_t regions_per_chunk,
-                                    uint64_t chunk_begin, uint64_t chunk_end) {
-  const uint64_t c = chunk_begin + blockIdx.x * static_cast<uint64_t>(blockDim.x) +
-                     threadIdx.x;
-  if (c >= chunk_end) return;
+// shift a raw CRC state by n regions of zeros (binary decomposition of n over
+// the 2^j-region tables)
+__device__ __forceinline__ uint32_t shift_regions(uint32_t x, uint32_t n) {
+  for (int j = 0; n != 0u; ++j, n >>= 1)
+    if (n & 1u) x = lin4(g_fcp_tab_regions + j * 1024, x);
+  return x;
+}
+
+// One WARP per chunk: combines the chunk's region values into the raw CRC of
+// the chunk (its last region zero-padded to 16 KiB; the host strips that
+// padding and applies init/xorout, fcp_finish_checksums).  Lane l owns up to
+// q = ceil(regions_per_chunk / 32) consecutive regions, right-aligned so that
+// lane 31 owns the chunk's last ones (empty leading lanes contribute the raw
+// CRC of nothing, 0, which no shift changes); q Horner steps, then a 5-level
+// tree.  One thread per chunk walked 128 dependent table lookups (17 us,
+// the floor of every small image).
+__global__ void __launch_bounds__(128) fcp_finalize_kernel(
+    const uint32_t* __restrict__ region_sums, uint32_t* __restrict__ chunk_sums,
+    uint64_t n_regions, uint32_t regions_per_chunk, uint64_t chunk_begin, uint64_t chunk_end) {
+  const int lane = threadIdx.x & 31;
+  const uint64_t c = chunk_begin + blockIdx.x * static_cast<uint64_t>(blockDim.x >> 5) +
+                     (threadIdx.x >> 5);
+  if (c >= chunk_end) return;  // uniform across the warp
   const uint64_t r0 = c * regions_per_chunk;
   uint64_t r1 = r0 + regions_per_chunk;
   if (r1 > n_regions) r1 = n_regions;
-  const uint32_t* F = g_fcp_tab + kTabF;
+  const int64_t n = static_cast<int64_t>(r1 - r0);
+  const int64_t q = (static_cast<int64_t>(regions_per_chunk) + 31) / 32;
+  int64_t hi = n - static_cast<int64_t>(31 - lane) * q;
+  int64_t lo = hi - q;
+  if (hi < 0) hi = 0;
+  if (lo < 0) lo = 0;
   uint32_t acc = 0;
-  // region values are independent of acc: fetch them 8 at a time so the
-  // serial Horner chain only waits on (L1-resident) table lookups
-  uint64_t r = r0;
-  for (; r + 8 <= r1; r += 8) {
-    uint32_t v[8];
+  const uint32_t* one = g_fcp_tab_regions;  // shift by one region
+  int64_t j = lo;
+  for (; j + 4 <= hi; j += 4) {  // values first: they do not depend on acc
+    uint32_t v[4];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) v[k] = __ldg(region_sums + r + k);
+    for (int k = 0; k < 4; ++k) v[k] = __ldg(region_sums + r0 + j + k);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc = lin4(F, acc) ^ v[k];
+    for (int k = 0; k < 4; ++k) acc = lin4(one, acc) ^ v[k];
   }
-  for (; r < r1; ++r) acc = lin4(F, acc) ^ __ldg(region_sums + r);
-  chunk_sums[c] = acc;
+  for (; j < hi; ++j) acc = lin4(one, acc) ^ __ldg(region_sums + r0 + j);
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const uint32_t recv = __shfl_up_sync(0xffffffffu, acc, 1u << k);
+    const uint32_t sh = shift_regions(recv, static_cast<uint32_t>(q) << k);
+    const uint32_t m = (2u << k) - 1u;
+    if ((static_cast<uint32_t>(lane) & m) == m) acc ^= sh;
+  }
+  if (lane == 31) chunk_sums[c] = acc;
 }
 
 }  // namespace fcpk
