@@ -38,8 +38,9 @@ GB = 1e9
 PCIE_GEN5_X16_GBS = 64.0
 # dram__bytes_read.sum + dram__bytes_write.sum over the pack launches of one save
 # (ncu --set full capture of this program, profiles/r01_ncu_pack_v3_summary.md)
-NCU_TRAFFIC_BYTES = {("gpt2-xl-1.5B-adamw-fp32", 0): 39.10e9}
-NCU_TRAFFIC_SOURCE = "profiles/r01_ncu_pack_v3_summary.md"
+NCU_TRAFFIC_BYTES = {("gpt2-xl-1.5B-adamw-fp32", 0): 39.10e9,      # profiles/r01_ncu_pack_v3_summary.md
+                     ("llama2-7b-fsdp8-shard", 0): 24.204e9}       # profiles/r02_ncu_pack_llama_summary.md
+NCU_TRAFFIC_SOURCE = "profiles/r02_ncu_pack_llama_summary.md, r01_ncu_pack_v3_summary.md"
 _REAL_STDOUT = sys.stdout
 
 WORKLOADS = {
