@@ -1035,9 +1035,15 @@ def run_ours(args, rank, local_rank, world):
     _barrier_sync(device)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
+    gate = eng._gate  # nodes with > 4 local ranks: device->host copies take turns (DmaGate)
+    plan.set_defer_copies(gate.enabled)
     for _ in range(K):
         plan.save_async(staging_ptr, addr, mode, _native.SUM_CRC32C, stream.cuda_stream)
+        if gate.enabled:
+            gate.acquire()
+            plan.release_copies()
         step_sums = plan.save_wait()
+        gate.release()
         launches += plan.last_launches()
         t = plan.timings()
         save_ms.append(t["total_ms"])
@@ -1145,6 +1151,8 @@ def run_ours(args, rank, local_rank, world):
                 "transfer_mode_chosen_at_run_time": (
                     dict(eng.tuner.rates, state=eng.tuner.state) if eng.tuner is not None else None),
                 "l2": "inputs (%.1f GB) larger than L2" % (B / GB), "note": note,
+                "dma_writers_at_a_time": (int(os.getenv("FCP_DMA_WRITERS", "4"))
+                                          if gate.enabled else world),
                 "host_link_peak_GBps_per_dir": PCIE_GEN5_X16_GBS},
             "save_blocking_s": save_blocking_s,
             "save_blocking_device_s": save_pack_ms / 1e3,

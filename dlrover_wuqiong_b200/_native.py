@@ -49,12 +49,14 @@ SYMBOLS = [
     ("fcp_chunk_xxh64", _i, [_vp, _u64, _u32, _vp, _vp]),
     ("fcp_launch_noalloc", _i, [_vp, _u64, _u64, _u32, _vp, _vp, _i, _i, _vp]),
     ("fcp_save_async", _i, [_vp, _vp, _vp, _i, _i, _vp]),
+    ("fcp_plan_set_defer_copies", _i, [_vp, _i]),
+    ("fcp_save_release_copies", _i, [_vp]),
     ("fcp_save_packed_wait", _i, [_vp]),
     ("fcp_save_wait", _i, [_vp, _vp]),
     ("fcp_restore", _i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
     ("fcp_restore_bounced", _i, [_vp, _vp, _vp, _i, _vp, _i, _vp]),
     ("fcp_restore_from_device", _i, [_vp, _vp, _i, _vp, _vp]),
-    ("fcp_restore_from_slices", _i, [_vp, _vp, _u64, _u64, _i, _vp, _i, _vp]),
+    ("fcp_restore_from_slices", _i, [_vp, _vp, _u64, _u64, _i, _vp, _i, _u64, _vp]),
     ("fcp_stage_range", _i, [_vp, _vp, _vp, _u64, _u64, _i, _i, _vp]),
     ("fcp_plan_set_window", _i, [_vp, _u64, _u64]),
     ("fcp_plan_timings", _i, [_vp, _vp]),
@@ -154,6 +156,12 @@ class Plan:
                    checksum=SUM_CRC32C, stream=0):
         check(lib().fcp_save_async(self._h, staging_ptr, host_ptr, mode, checksum, stream))
 
+    def set_defer_copies(self, defer):
+        check(lib().fcp_plan_set_defer_copies(self._h, 1 if defer else 0))
+
+    def release_copies(self):
+        check(lib().fcp_save_release_copies(self._h))
+
     def save_packed_wait(self):
         check(lib().fcp_save_packed_wait(self._h))
 
@@ -192,7 +200,7 @@ class Plan:
             exp.ctypes.data if exp is not None else None, stream))
 
     def restore_from_slices(self, bases, slice_bytes, checksum=SUM_CRC32C, expected=None,
-                            read_prefetch=False, stream=0):
+                            read_prefetch=False, first_slice=0, stream=0):
         """bases[s]: address image byte 0 would have in the buffer that holds
         slice s (see fcp.h)."""
         a = np.ascontiguousarray(bases, dtype=np.uint64)
@@ -203,7 +211,8 @@ class Plan:
                 raise ValueError("expected %d checksums, got %d" % (self.num_chunks, len(exp)))
         check(lib().fcp_restore_from_slices(
             self._h, a.ctypes.data, len(a), slice_bytes, checksum,
-            exp.ctypes.data if exp is not None else None, 1 if read_prefetch else 0, stream))
+            exp.ctypes.data if exp is not None else None, 1 if read_prefetch else 0,
+            first_slice % max(len(a), 1), stream))
 
     def stage_range(self, host_ptr, staging_ptr, byte_begin, byte_end, registered=False,
                     n_workers=0, stream=0):

@@ -102,7 +102,7 @@ constexpr size_t kSmemBig = sizeof(uint32_t) * (1024 * 32 + 1024 * 16 + 5120);
 constexpr size_t kSmemSmall = sizeof(uint32_t) * (1024 + 1024 + 5120);
 
 template <bool PACK, bool CRC, bool SLICED = false>
-int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
+int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_region = 0) {
   fcpk::Args a = a_in;
   const uint64_t regions = a.region_end - a.region_begin;
   if (regions == 0) return 0;
@@ -110,6 +110,7 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
   // longest run that still leaves every warp of a full grid >= 4 visits
   uint64_t run = regions / (static_cast<uint64_t>(sms) * 32 * 4);
   a.run = static_cast<uint32_t>(run < 1 ? 1 : run > fcpk::kMaxRun ? fcpk::kMaxRun : run);
+  a.rotate = (first_region - a.region_begin) / a.run;  // in runs (sliced scatter only)
   static const bool no_pf = getenv("FCP_DEBUG_NO_PREFETCH") != nullptr;  // tuning aid
   if (no_pf) a.flags |= fcpk::kNoPrefetch;
   // Big shape: one 1024-thread CTA per SM with the conflict-free (32x
@@ -155,11 +156,11 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st) {
 }
 
 int launch_any(const fcpk::Args& a, int direction, int checksum, int dev,
-               cudaStream_t st) {
+               cudaStream_t st, uint64_t first_region = 0) {
   if (a.slice_base != nullptr) {  // scatter only
     if (direction != 1) return fail(-EINVAL, "a sliced image can only be scattered");
-    return checksum ? launch_dir<false, true, true>(a, dev, st)
-                    : launch_dir<false, false, true>(a, dev, st);
+    return checksum ? launch_dir<false, true, true>(a, dev, st, first_region)
+                    : launch_dir<false, false, true>(a, dev, st, first_region);
   }
   if (direction == 0)
     return checksum ? launch_dir<true, true>(a, dev, st)
@@ -223,6 +224,13 @@ struct fcp_plan {
   bool save_in_flight = false;
   int save_mode = 0;
   uint64_t win_begin = 0, win_end = ~0ull;  // chunk window of fcp_save_async
+  // staged save whose device->host copies are enqueued apart from the pack
+  bool defer_copies = false, copies_pending = false;
+  void* sv_staging = nullptr;
+  void* sv_host = nullptr;
+  uint8_t* sv_alias = nullptr;
+  int sv_checksum = 0;
+  std::vector<std::pair<uint64_t, uint64_t>> sv_slices;
   const uint8_t** d_slice_bases = nullptr;  // table of fcp_restore_from_slices
   uint64_t slice_bases_cap = 0;
   // pinned bounce ring of fcp_restore_bounced: 2 slots per worker
@@ -725,6 +733,38 @@ int fcp_read_checksums(fcp_plan* p, uint32_t* out, void* stream) {
 }
 
 // ======================================================== transfer engine
+// Device->host leg of a staged save: slice k leaves as soon as its pack
+// kernel is done (ev_slice[k]); the chunk sums follow the finalize kernel.
+static int enqueue_save_copies(fcp_plan* p) {
+  for (size_t s = 0; s < p->sv_slices.size(); ++s) {
+    const uint64_t b0 = p->sv_slices[s].first * p->chunk_bytes;
+    uint64_t b1 = p->sv_slices[s].second * static_cast<uint64_t>(p->chunk_bytes);
+    if (b1 > p->total) b1 = p->total;
+    FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_slice[s], 0));
+    if (p->save_mode == FCP_MODE_STAGED_KERNEL) {
+      static const int ctas = getenv("FCP_COPY_CTAS") ? atoi(getenv("FCP_COPY_CTAS")) : 32;
+      const uint64_t n = b1 - b0;  // b0 is a multiple of the chunk size
+      fcpk::fcp_copy_kernel<<<ctas > 0 ? ctas : 32, 256, 0, p->copy_stream>>>(
+          static_cast<const uint8_t*>(p->sv_staging) + b0, p->sv_alias + b0, n / 32, n % 32);
+      FCP_CUDA(cudaGetLastError());
+      p->last_launches++;
+    } else {
+      int rc = copy_image_range(p, static_cast<uint8_t*>(p->sv_staging),
+                                static_cast<uint8_t*>(p->sv_host), b0, b1, true,
+                                p->copy_stream);
+      if (rc) return rc;
+    }
+  }
+  FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_kern_e, 0));
+  if (p->sv_checksum && p->n_chunks)
+    FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
+                             sizeof(uint32_t) * p->n_chunks,
+                             cudaMemcpyDeviceToHost, p->copy_stream));
+  FCP_CUDA(cudaEventRecord(p->ev_done, p->copy_stream));
+  p->copies_pending = false;
+  return 0;
+}
+
 int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
                    int checksum, void* stream) {
   if (!p) return fail(-EINVAL, "plan is NULL");
@@ -761,31 +801,14 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
         return fail(-ENOTSUP, "host pointer is not usable from the device as is");
       host_alias = static_cast<uint8_t*>(a0);
     }
-    const auto slices = make_slices(p, true, p->win_begin, p->win_end);
-    rc = plan_slice_events(p, slices.size());
+    p->sv_slices = make_slices(p, true, p->win_begin, p->win_end);
+    rc = plan_slice_events(p, p->sv_slices.size());
     if (rc) return rc;
-    for (size_t s = 0; s < slices.size(); ++s) {
-      const uint64_t cb = slices[s].first, ce = slices[s].second;
-      rc = plan_launch(p, staging, 0, checksum, cb, ce, st, false);
+    for (size_t s = 0; s < p->sv_slices.size(); ++s) {
+      rc = plan_launch(p, staging, 0, checksum, p->sv_slices[s].first,
+                       p->sv_slices[s].second, st, false);
       if (rc) return rc;
       FCP_CUDA(cudaEventRecord(p->ev_slice[s], st));
-      const uint64_t b0 = cb * p->chunk_bytes;
-      uint64_t b1 = ce * static_cast<uint64_t>(p->chunk_bytes);
-      if (b1 > p->total) b1 = p->total;
-      FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_slice[s], 0));
-      if (mode == FCP_MODE_STAGED_KERNEL) {
-        static const int ctas = getenv("FCP_COPY_CTAS") ? atoi(getenv("FCP_COPY_CTAS")) : 32;
-        const uint64_t n = b1 - b0;  // b0 is a multiple of the chunk size
-        fcpk::fcp_copy_kernel<<<ctas > 0 ? ctas : 32, 256, 0, p->copy_stream>>>(
-            static_cast<const uint8_t*>(staging) + b0, host_alias + b0, n / 32, n % 32);
-        FCP_CUDA(cudaGetLastError());
-        p->last_launches++;
-      } else {
-        rc = copy_image_range(p, static_cast<uint8_t*>(staging),
-                              static_cast<uint8_t*>(host_dst), b0, b1, true,
-                              p->copy_stream);
-        if (rc) return rc;
-      }
     }
     // the sources are free once the last pack kernel is done; combining the
     // region values into chunk values only touches the plan's own buffers
@@ -797,9 +820,17 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
                            p->chunk_bytes / FCP_REGION_BYTES, wb, we, st);
       if (rc) return rc;
       p->last_launches++;
-      FCP_CUDA(cudaEventRecord(p->ev_kern_e, st));
-      FCP_CUDA(cudaStreamWaitEvent(p->copy_stream, p->ev_kern_e, 0));
     }
+    FCP_CUDA(cudaEventRecord(p->ev_kern_e, st));
+    p->sv_staging = staging;
+    p->sv_host = host_dst;
+    p->sv_alias = host_alias;
+    p->sv_checksum = checksum;
+    p->save_mode = mode;
+    p->last_has_sums = checksum != 0;
+    p->save_in_flight = true;
+    p->copies_pending = true;
+    return p->defer_copies ? 0 : enqueue_save_copies(p);
   }
   if (checksum && p->n_chunks)
     FCP_CUDA(cudaMemcpyAsync(p->h_chunk_sums, p->d_chunk_sums,
@@ -812,6 +843,22 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
   return 0;
 }
 
+int fcp_plan_set_defer_copies(fcp_plan* p, int defer) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (p->save_in_flight) return fail(-EBUSY, "a save is in flight");
+  p->defer_copies = defer != 0;
+  return 0;
+}
+
+int fcp_save_release_copies(fcp_plan* p) {
+  if (!p) return fail(-EINVAL, "plan is NULL");
+  if (!p->save_in_flight) return fail(-EINVAL, "no save in flight");
+  if (!p->copies_pending) return 0;
+  DeviceGuard g(p->device);
+  if (!g.ok) return fail(-EIO, "cannot select device %d", p->device);
+  return enqueue_save_copies(p);
+}
+
 int fcp_save_packed_wait(fcp_plan* p) {
   if (!p) return fail(-EINVAL, "plan is NULL");
   if (!p->save_in_flight) return fail(-EINVAL, "no save in flight");
@@ -822,6 +869,8 @@ int fcp_save_packed_wait(fcp_plan* p) {
 int fcp_save_wait(fcp_plan* p, uint32_t* chunk_sums) {
   if (!p) return fail(-EINVAL, "plan is NULL");
   if (!p->save_in_flight) return fail(-EINVAL, "no save in flight");
+  if (p->copies_pending)
+    return fail(-EINVAL, "the copies of this save were deferred: call fcp_save_release_copies");
   p->save_in_flight = false;
   FCP_CUDA(cudaEventSynchronize(p->ev_done));
   FCP_CUDA(cudaEventElapsedTime(&p->t_kernel_ms, p->ev_begin, p->ev_packed));
@@ -1100,7 +1149,7 @@ int fcp_stage_range(fcp_plan* p, const void* host_src, void* staging,
 int fcp_restore_from_slices(fcp_plan* p, const void* const* slice_bases,
                             uint64_t n_slices, uint64_t slice_bytes, int checksum,
                             const uint32_t* expected, int read_prefetch,
-                            void* stream) {
+                            uint64_t first_slice, void* stream) {
   if (!p) return fail(-EINVAL, "plan is NULL");
   if (expected && !checksum)
     return fail(-EINVAL, "expected sums given but checksum disabled");
@@ -1138,7 +1187,7 @@ int fcp_restore_from_slices(fcp_plan* p, const void* const* slice_bases,
     a.slice_base = p->d_slice_bases;
     a.slice_regions = static_cast<uint32_t>(slice_bytes / FCP_REGION_BYTES);
     if (!read_prefetch) a.flags |= fcpk::kNoPrefetch;
-    rc = launch_any(a, 1, checksum, p->device, st);
+    rc = launch_any(a, 1, checksum, p->device, st, first_slice * a.slice_regions);
     if (rc) return rc;
     p->last_launches++;
     if (checksum) {

@@ -291,6 +291,7 @@ struct Args {
   // of the slices that point at it (a region never reads outside itself).
   const uint8_t* const* slice_base = nullptr;  // device array, or nullptr
   uint32_t slice_regions = 0;
+  uint64_t rotate = 0;  // sliced scatter: run index this launch starts from
 };
 constexpr uint32_t kNoPrefetch = 1u;
 

@@ -208,7 +208,11 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   while (run < n_runs) {
    uint32_t drawn = 0;
    if (work != nullptr && lane == 0) drawn = atomicAdd(&work[0], 1u);
-   const uint64_t run_begin = a.region_begin + run * kRun;
+   // a sliced scatter starts at a rank-specific slice (a.rotate runs in):
+   // the ranks of a group then read different peers at any moment instead of
+   // all draining the same peer's NVLink egress together
+   const uint64_t run_at = !SLICED ? run : (run + a.rotate) % n_runs;
+   const uint64_t run_begin = a.region_begin + run_at * kRun;
    const uint64_t run_end =
        run_begin + kRun < a.region_end ? run_begin + kRun : a.region_end;
    Cur c;

@@ -233,7 +233,11 @@ def restore_replicated(handler, into, device, group=None):
             per_bytes = -(-n_chunks // len(stripes)) * chunk  # as plan_providers cuts them
             expected = checksums_from_meta(entry, total, chunk)
             local = all(p == me for lo, hi, p, _ in stripes if hi > lo)
-            engine.restore_from_slices(total, bases, per_bytes, expected, local=local)
+            # start one stripe past my own: at any moment the ranks of the
+            # node then read different peers
+            ranks_here = sorted(r for r, f in enumerate(facts) if f["host"] == mine["host"])
+            engine.restore_from_slices(total, bases, per_bytes, expected, local=local,
+                                       first_slice=ranks_here.index(me) + 1)
             handler.last_stats = dict(engine.stats)
     except Exception as e:  # noqa: BLE001
         error = error or e

@@ -82,6 +82,63 @@ class SaveLegTuner(object):
                         "copy kernel" if self.choice == _native.MODE_STAGED_KERNEL else "copy engine")
 
 
+class DmaGate(object):
+    """Turn-taking for the device->host copies of the ranks of one node.
+
+    Measured on an 8-GPU host (tools/hostlink_matrix.py,
+    profiles/r02_hostlink.md): copy-engine writes into host memory reach
+    90 GB/s with all 8 ranks writing at once but 102 GB/s when 4 write at a
+    time (2 at a time: 85, one: 57); reads scale to 186 GB/s with all 8.  So
+    on nodes with more than `FCP_DMA_WRITERS` (default 4) local ranks, a
+    rank's copies wait for one of that many slots: rank r shares slot
+    r mod k with the ranks k apart and they alternate.  A slot is an advisory
+    lock on a file in /dev/shm; it is only held while the copies run, never
+    while the training thread is blocked (the pack kernels run first)."""
+
+    def __init__(self, local_rank, local_world):
+        k = int(os.getenv("FCP_DMA_WRITERS", "4"))
+        self.enabled = 0 < k < local_world
+        self._fd = -1
+        self.wait_s = 0.0
+        if self.enabled:
+            run_id = os.getenv("TORCHELASTIC_RUN_ID", "")
+            path = "/dev/shm/%sfcp_dma_slot_%d" % (run_id + "_" if run_id else "", local_rank % k)
+            try:
+                self._fd = os.open(path, os.O_CREAT | os.O_RDWR, 0o600)
+            except OSError as e:
+                logger.warning("cannot open %s (%s): device->host copies are not paced", path, e)
+                self.enabled = False
+
+    def acquire(self):
+        if self.enabled:
+            import fcntl
+            t0 = time.perf_counter()
+            fcntl.flock(self._fd, fcntl.LOCK_EX)
+            self.wait_s = time.perf_counter() - t0
+
+    def release(self):
+        if self.enabled:
+            import fcntl
+            fcntl.flock(self._fd, fcntl.LOCK_UN)
+
+    def close(self):
+        if self._fd >= 0:
+            os.close(self._fd)
+            self._fd = -1
+
+
+def default_bounce_workers():
+    """Host threads that feed the pinned ring of an unpinned restore: half the
+    cores, shared by the local ranks, between 2 and 8 (8 ranks x 8 threads on
+    a 32-core host only fought each other)."""
+    env = int(os.getenv("FCP_BOUNCE_WORKERS", "0"))
+    if env > 0:
+        return env
+    cores = os.cpu_count() or 1
+    local_world = max(1, int(os.getenv("LOCAL_WORLD_SIZE", "1") or 1))
+    return max(2, min(8, cores // (2 * local_world)))
+
+
 def buffer_address(buf):
     """Address of a writable buffer object (mmap / memoryview)."""
     return ctypes.addressof(ctypes.c_char.from_buffer(buf))
@@ -180,6 +237,8 @@ class DeviceShardEngine(object):
         self._mapping = None
         self._mapping_job = None  # background registration after a cold restore
         self._keepalive = []
+        self._gate = DmaGate(int(os.getenv("LOCAL_RANK", "0") or 0),
+                             int(os.getenv("LOCAL_WORLD_SIZE", "1") or 1))
         self._save_bytes = 0
         self._window = None
         self._restore_host_leaves = []
@@ -372,6 +431,8 @@ class DeviceShardEngine(object):
             staging_ptr = self._staging.data_ptr() if self._staging is not None else None
             if self.tuner is not None:
                 self.mode = self.tuner.mode()
+            # paced copies (DmaGate): pack now, copy when this rank has a slot
+            plan.set_defer_copies(self._gate.enabled and self.mode != _native.MODE_DIRECT)
             try:
                 plan.save_async(staging_ptr, addr, self.mode, self.checksum, stream.cuda_stream)
             except _native.FcpError:
@@ -390,8 +451,18 @@ class DeviceShardEngine(object):
             self._plan.save_packed_wait()
 
     def save_finish(self):
-        with self._nvtx("fcp.d2h_wait"):
-            sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
+        paced = self._gate.enabled and self.mode != _native.MODE_DIRECT
+        if paced:
+            self._gate.acquire()
+        try:
+            if paced:
+                self._plan.release_copies()
+            with self._nvtx("fcp.d2h_wait"):
+                sums = self._plan.save_wait(want_sums=self.checksum != _native.SUM_NONE)
+        finally:
+            if paced:
+                self._gate.release()
+        self.stats["dma_slot_wait_s"] = self._gate.wait_s if paced else 0.0
         self._keepalive = []
         self.stats.update(self._plan.timings())
         self.stats["save_mode"] = self.mode
@@ -449,8 +520,7 @@ class DeviceShardEngine(object):
             if transient:
                 if total:
                     plan.restore_bounced(buffer_address(buf), staging_ptr, checksum, expected,
-                                         int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
-                                         stream.cuda_stream)
+                                         default_bounce_workers(), stream.cuda_stream)
                 self.stats["restore_path"] = "bounced_file"
             elif (cold and total and self.mode != _native.MODE_DIRECT
                     and os.getenv("FCP_COLD_RESTORE", "bounce") == "bounce"):
@@ -460,8 +530,7 @@ class DeviceShardEngine(object):
                     self._mapping.close()
                     self._mapping = None
                 plan.restore_bounced(buffer_address(buf), staging_ptr, checksum, expected,
-                                     int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
-                                     stream.cuda_stream)
+                                     default_bounce_workers(), stream.cuda_stream)
                 self.stats["restore_path"] = "bounced"
                 pin_later = True
             else:
@@ -539,12 +608,13 @@ class DeviceShardEngine(object):
                 self._plan.set_copy_piece_bytes(self._piece_bytes())
             stream = torch.cuda.current_stream(self.device)
             self._plan.stage_range(addr, self._staging.data_ptr(), lo, hi, registered=pinned,
-                                   n_workers=int(os.getenv("FCP_BOUNCE_WORKERS", "0")),
+                                   n_workers=default_bounce_workers(),
                                    stream=stream.cuda_stream)
             self.stats["stage_path"] = "registered" if pinned else "bounced"
             self.stats["stage_ms"] = self._plan.timings()["total_ms"]
 
-    def restore_from_slices(self, total, bases, slice_bytes, expected=None, local=False):
+    def restore_from_slices(self, total, bases, slice_bytes, expected=None, local=False,
+                            first_slice=0):
         """One scatter launch over an image whose slice s is read through
         bases[s] (own staging or peers' staging mapped with CUDA IPC); call
         prepare_restore first.  `local`: every base is this GPU's memory."""
@@ -552,7 +622,8 @@ class DeviceShardEngine(object):
             stream = torch.cuda.current_stream(self.device)
             checksum = self.checksum if expected is not None else _native.SUM_NONE
             self._plan.restore_from_slices(bases, slice_bytes, checksum, expected,
-                                           read_prefetch=local, stream=stream.cuda_stream)
+                                           read_prefetch=local, first_slice=first_slice,
+                                           stream=stream.cuda_stream)
             self._stage_host_leaves(self._restore_host_leaves, to_device=False)
             self._restore_host_leaves = []
             self.stats.update(self._plan.timings())
@@ -578,6 +649,7 @@ class DeviceShardEngine(object):
         self._staging = None
         self._arena_dev = None
         self._arena_pin = None
+        self._gate.close()
 
 
 def checksums_to_meta(sums, chunk_bytes, xxh64=None, host_leaves=None):

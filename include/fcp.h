@@ -212,6 +212,16 @@ int fcp_launch_noalloc(const fcp_desc* descs_dev, uint64_t n,
  * (fcp_save_packed_wait); FCP_MODE_DIRECT ignores `staging`.                */
 int fcp_save_async(fcp_plan* plan, void* staging, void* host_dst, int mode,
                    int checksum, void* stream);
+/* Split a staged save in two: with defer != 0, fcp_save_async launches the
+ * pack kernels only and fcp_save_release_copies later enqueues the
+ * device->host copies (fcp_save_wait refuses to run before that).  Lets the
+ * caller take a turn on a shared host: on an 8-GPU node 4 ranks writing at a
+ * time move 102 GB/s into host memory, all 8 at once 90 GB/s (measured,
+ * profiles/r02_hostlink.md); the training-blocking part of the save is not
+ * delayed by the wait for a turn.  No counterpart in the reference (its
+ * copies are synchronous, SAVER:197-206).                                   */
+int fcp_plan_set_defer_copies(fcp_plan* plan, int defer);
+int fcp_save_release_copies(fcp_plan* plan);
 /* Wait until the pack kernel has consumed the live tensors (the training-
  * blocking part).                                                           */
 int fcp_save_packed_wait(fcp_plan* plan);
@@ -262,11 +272,16 @@ int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
  * launch pulls every slice over NVLink with plain per-thread loads, verifies
  * the CRC-32C of every chunk and unpacks into the live tensors; pass
  * read_prefetch = 0 when any base is peer memory (see
- * fcp_plan_set_read_prefetch).  Synchronous.                                */
+ * fcp_plan_set_read_prefetch).  The launch works through the image starting
+ * at slice `first_slice` and wraps around: give every rank of the group a
+ * different one (its own index + 1) so that at any moment the ranks read
+ * different peers instead of all draining one peer's NVLink egress
+ * (measured, 8 ranks: 174 -> see DESIGN.md §6).  Synchronous.              */
 int fcp_restore_from_slices(fcp_plan* plan, const void* const* slice_bases,
                             uint64_t n_slices, uint64_t slice_bytes,
                             int checksum, const uint32_t* expected,
-                            int read_prefetch, void* stream);
+                            int read_prefetch, uint64_t first_slice,
+                            void* stream);
 
 /* Host -> staging copy of image bytes [byte_begin, byte_end) only, no
  * kernel: the host-link leg of a striped restore, where every rank of a

@@ -228,3 +228,35 @@ def test_stage_range_moves_exactly_the_range(registered):
     assert got[lo:hi].tobytes() == src.numpy()[lo:hi].tobytes()
     assert (got[:lo] == 0xC3).all() and (got[hi:total] == 0xC3).all()
     plan.close()
+
+
+def test_deferred_copies_of_a_staged_save():
+    """fcp_plan_set_defer_copies: pack now, copy when told to (ranks of a big
+    node take turns writing into host memory); same bytes, same sums."""
+    dev = torch.device("cuda", 0)
+    tensors, offs, sizes, total = _random_case(77, 30, 700000, dev)
+    image = _oracle_image(tensors, offs, sizes, total)
+    plan = _native.Plan(_native.make_descs([t.data_ptr() for t in tensors], offs, sizes),
+                        total, 0, CHUNK)
+    staging = torch.zeros(plan.staging_bytes, dtype=torch.uint8, device=dev)
+    host = torch.full((total,), 0x33, dtype=torch.uint8).pin_memory()
+    stream = torch.cuda.current_stream().cuda_stream
+    plan.set_defer_copies(True)
+    plan.save_async(staging.data_ptr(), host.data_ptr(), _native.MODE_STAGED,
+                    _native.SUM_CRC32C, stream)
+    plan.save_packed_wait()
+    torch.cuda.synchronize()
+    assert int(host[0]) == 0x33 and int(host[total - 1]) == 0x33  # nothing copied yet
+    with pytest.raises(_native.FcpError, match="deferred"):
+        plan.save_wait()
+    plan.release_copies()
+    sums = plan.save_wait()
+    assert host.numpy().tobytes() == image.tobytes()
+    assert sums.tolist() == oracle.chunk_crc32c(image, CHUNK).tolist()
+    plan.set_defer_copies(False)  # and the undeferred path still works on the same plan
+    host.fill_(0)
+    plan.save_async(staging.data_ptr(), host.data_ptr(), _native.MODE_STAGED,
+                    _native.SUM_CRC32C, stream)
+    assert plan.save_wait().tolist() == sums.tolist()
+    assert host.numpy().tobytes() == image.tobytes()
+    plan.close()

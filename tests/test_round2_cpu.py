@@ -226,3 +226,35 @@ def test_plan_providers():
     got = plan_providers([f("a", shm=5)] * 4, 5, 3 * MB, chunk)
     assert [s[:2] for s in got["a"]] == [(0, 2 * MB), (2 * MB, 3 * MB), (3 * MB, 3 * MB),
                                          (3 * MB, 3 * MB)]
+
+
+# ------------------------------------------------------- DMA turn-taking
+def test_dma_gate_slots(monkeypatch):
+    import threading
+    import time
+    from dlrover_wuqiong_b200.transfer import DmaGate, default_bounce_workers
+    monkeypatch.setenv("FCP_DMA_WRITERS", "2")
+    assert not DmaGate(0, 2).enabled and not DmaGate(1, 1).enabled  # few ranks: no pacing
+    a, b, c = DmaGate(0, 4), DmaGate(2, 4), DmaGate(1, 4)  # ranks 0 and 2 share slot 0
+    assert a.enabled and b.enabled and c.enabled
+    a.acquire()
+    c.acquire()  # another slot: does not wait
+    got = []
+    t = threading.Thread(target=lambda: (b.acquire(), got.append(time.perf_counter()), b.release()))
+    t0 = time.perf_counter()
+    t.start()
+    time.sleep(0.3)
+    assert not got  # rank 2 waits for rank 0's turn to end
+    a.release()
+    t.join(5)
+    assert got and got[0] - t0 >= 0.3 and b.wait_s >= 0.25
+    c.release()
+    for g in (a, b, c):
+        g.close()
+    monkeypatch.setenv("FCP_DMA_WRITERS", "0")
+    assert not DmaGate(0, 8).enabled
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    monkeypatch.delenv("FCP_BOUNCE_WORKERS", raising=False)
+    assert 2 <= default_bounce_workers() <= 8
+    monkeypatch.setenv("FCP_BOUNCE_WORKERS", "5")
+    assert default_bounce_workers() == 5
