@@ -205,23 +205,18 @@ def restore_replicated(handler, into, device, group=None):
         exported = _native.ipc_export(staging.data_ptr())
     handles = [None] * world
     dist.all_gather_object(handles, exported, group=group)
-    opened = {}
     bases = []
-    sums = None
     try:
         if error is None:
             for lo, hi, provider, _ in stripes:
                 if provider == me or hi <= lo:
                     bases.append(staging.data_ptr())
                     continue
-                if provider not in opened:
-                    if handles[provider] is None:
-                        raise RuntimeError("rank %d cannot serve its stripe" % provider)
-                    handle, offset = handles[provider]
-                    with torch.cuda.device(dev):
-                        opened[provider] = (_native.ipc_open(handle), offset)
-                base, offset = opened[provider]
-                bases.append(base + offset)
+                if handles[provider] is None:
+                    raise RuntimeError("rank %d cannot serve its stripe" % provider)
+                handle, offset = handles[provider]
+                # (mappings of peers' staging are kept by the engine: see peer_base)
+                bases.append(engine.peer_base(provider, handle) + offset)
     except Exception as e:  # noqa: BLE001
         error = error or e
     # everybody's stripe is complete and exported before anybody reads
@@ -244,11 +239,6 @@ def restore_replicated(handler, into, device, group=None):
     t_done = time.perf_counter()
     # nobody lets go of its staging before everybody is done reading
     all_ok = _vote(error is None, dev, group)
-    for base, _ in opened.values():
-        try:
-            _native.ipc_close(base)
-        except Exception as e:  # noqa: BLE001
-            logger.warning("ipc_close failed: %s", e)
     if error is not None or not all_ok:
         # whatever went wrong, do not offer this staging again: the next
         # attempt starts from the shm image

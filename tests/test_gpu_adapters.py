@@ -312,3 +312,76 @@ def test_cpu_views_of_a_pinned_segment_copy_to_the_gpu(saver_env):
             assert torch.equal(up, v), k
         del views
         ckpt.close()
+
+
+def test_hf_flash_ckpt_trainer_on_cuda(saver_env, monkeypatch):
+    """FlashCkptTrainer (stand-in Trainer, see tests/test_adapters_cpu.py) with
+    the model and optimizer on the GPU: every torch.save of the Trainer is
+    captured, the captured state goes through the pack kernel (shm bytes ==
+    oracle image, CRC recorded) and the agent persists files that load back
+    equal.  The reference's HF adapter has no restore-from-memory path
+    (hf_trainer.py:123-257 only saves), so there is none to test."""
+    import sys
+    import time
+    import types
+
+    import dlrover_wuqiong_b200.flash_checkpoint.hf_trainer as hf
+    dev = torch.device("cuda", 0)
+
+    class Trainer(object):
+        def __init__(self, model, args):
+            self.model, self.model_wrapped, self.args = model, model, args
+            self.optimizer = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
+            self.state = types.SimpleNamespace(global_step=0, best_model_checkpoint=None)
+            self.is_deepspeed_enabled = self.is_fsdp_enabled = False
+
+        def _get_output_dir(self, trial=None):
+            return self.args.output_dir
+
+        def _save_checkpoint(self, model, trial):
+            out = os.path.join(self.args.output_dir, "checkpoint-%d" % self.state.global_step)
+            os.makedirs(out, exist_ok=True)
+            torch.save(model.state_dict(), os.path.join(out, "pytorch_model.bin"))
+            torch.save(self.optimizer.state_dict(), os.path.join(out, "optimizer.pt"))
+            torch.save({"cpu": torch.get_rng_state()}, os.path.join(out, "rng_state.pth"))
+
+        def _sorted_checkpoints(self, use_mtime=False, output_dir=None):
+            return []
+
+    fake = types.ModuleType("transformers")
+    fake.Trainer = Trainer
+    utils = types.ModuleType("transformers.trainer_utils")
+    utils.PREFIX_CHECKPOINT_DIR = "checkpoint"
+    fake.trainer_utils = utils
+    monkeypatch.setitem(sys.modules, "transformers", fake)
+    monkeypatch.setitem(sys.modules, "transformers.trainer_utils", utils)
+    monkeypatch.setattr(hf, "_TRAINER_CLS", None)
+    with tempfile.TemporaryDirectory() as tmpdir:
+        args = types.SimpleNamespace(output_dir=tmpdir, save_safetensors=True, save_total_limit=None)
+        model = Net().to(dev)
+        trainer = hf.FlashCkptTrainer(model, args)
+        (model.fc2(model.fc1(torch.randn(2, 257, device=dev))).sum()
+         + model.big(torch.randn(2, 1024, device=dev)).sum()).backward()
+        trainer.optimizer.step()
+        trainer.state.global_step = 7
+        trainer._save_checkpoint(model, None)
+        flash = trainer.flash_checkpointer
+        handler = flash.async_save_engine._shm_handler
+        captured = {k: v for k, v in flash.ckpt_agent.state_dict.items()
+                    if k.endswith((".bin", ".pt", ".pth"))}  # (the engine adds its config leaf)
+        assert set(captured) == {"pytorch_model.bin", "optimizer.pt", "rng_state.pth"}
+        out = os.path.join(tmpdir, "checkpoint-7")
+        tracker = os.path.join(tmpdir, "dlrover_latest.txt")
+        t0 = time.time()
+        while time.time() - t0 < 60 and not (os.path.exists(tracker)
+                                             and open(tracker).read() == "7"):
+            time.sleep(0.1)
+        assert open(tracker).read() == "7"
+        _assert_shm_is_oracle_image(handler, captured)
+        assert handler.last_stats.get("save_mode") is not None  # through libfcp
+        weights = torch.load(os.path.join(out, "pytorch_model.bin"), weights_only=False)
+        assert torch.equal(weights["big.weight"], model.big.weight.cpu())
+        optim = torch.load(os.path.join(out, "optimizer.pt"), weights_only=False)
+        assert torch.equal(optim["state"][0]["momentum_buffer"],
+                           trainer.optimizer.state_dict()["state"][0]["momentum_buffer"].cpu())
+        flash.async_save_engine.close()
