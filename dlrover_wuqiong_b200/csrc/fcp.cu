@@ -102,7 +102,8 @@ constexpr size_t kSmemBig = sizeof(uint32_t) * (1024 * 32 + 1024 * 16 + 5120);
 constexpr size_t kSmemSmall = sizeof(uint32_t) * (1024 + 1024 + 5120);
 
 template <bool PACK, bool CRC, bool SLICED = false>
-int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_region = 0) {
+int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_region = 0,
+               bool* fused = nullptr) {
   fcpk::Args a = a_in;
   const uint64_t regions = a.region_end - a.region_begin;
   if (regions == 0) return 0;
@@ -120,6 +121,10 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_
   static const bool force_big = getenv("FCP_DEBUG_FORCE_BIG") != nullptr;  // tuning aid
   const uint64_t runs = ceil_div(regions, a.run);
   const bool big = (CRC || force_big) && runs >= static_cast<uint64_t>(sms) * 32;
+  // the last-warp-out finalize exists in the 256-thread shape only, needs the
+  // plan's counters and a checksum
+  if (big || !CRC || a.work == nullptr) a.flags &= ~fcpk::kFusedFinalize;
+  if (fused) *fused = (a.flags & fcpk::kFusedFinalize) != 0;
   if (big) {
     auto kern = fcpk::fcp_kernel<PACK, CRC, 32, kBigThreads, SLICED>;
     if (!g_attr_done[dev]) {
@@ -156,17 +161,18 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_
 }
 
 int launch_any(const fcpk::Args& a, int direction, int checksum, int dev,
-               cudaStream_t st, uint64_t first_region = 0) {
+               cudaStream_t st, uint64_t first_region = 0, bool* fused = nullptr) {
+  if (fused) *fused = false;
   if (a.slice_base != nullptr) {  // scatter only
     if (direction != 1) return fail(-EINVAL, "a sliced image can only be scattered");
-    return checksum ? launch_dir<false, true, true>(a, dev, st, first_region)
-                    : launch_dir<false, false, true>(a, dev, st, first_region);
+    return checksum ? launch_dir<false, true, true>(a, dev, st, first_region, fused)
+                    : launch_dir<false, false, true>(a, dev, st, first_region, fused);
   }
   if (direction == 0)
-    return checksum ? launch_dir<true, true>(a, dev, st)
-                    : launch_dir<true, false>(a, dev, st);
-  return checksum ? launch_dir<false, true>(a, dev, st)
-                  : launch_dir<false, false>(a, dev, st);
+    return checksum ? launch_dir<true, true>(a, dev, st, 0, fused)
+                    : launch_dir<true, false>(a, dev, st, 0, fused);
+  return checksum ? launch_dir<false, true>(a, dev, st, 0, fused)
+                  : launch_dir<false, false>(a, dev, st, 0, fused);
 }
 
 int launch_finalize(const uint32_t* region_sums, uint32_t* chunk_sums,
@@ -287,13 +293,21 @@ int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
   const uint32_t rpc = p->chunk_bytes / FCP_REGION_BYTES;
   uint64_t rb = cb * rpc, re = ce * rpc;
   if (re > p->n_regions) re = p->n_regions;
+  bool fused = false;
   if (re > rb) {
-    int rc = launch_any(plan_args(p, packed, rb, re), direction, checksum,
-                        p->device, st);
+    fcpk::Args a = plan_args(p, packed, rb, re);
+    if (checksum && finalize && ce - cb <= fcpk::kFuseMaxChunks) {
+      a.flags |= fcpk::kFusedFinalize;  // (kept only for the small shape, see launch_dir)
+      a.chunk_sums = p->d_chunk_sums;
+      a.regions_per_chunk = rpc;
+      a.chunk_begin = cb;
+      a.chunk_end = ce < p->n_chunks ? ce : p->n_chunks;
+    }
+    int rc = launch_any(a, direction, checksum, p->device, st, 0, &fused);
     if (rc) return rc;
     p->last_launches++;
   }
-  if (checksum && finalize && ce > cb) {
+  if (checksum && finalize && ce > cb && !fused) {
     int rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
                              rpc, cb, ce, st);
     if (rc) return rc;

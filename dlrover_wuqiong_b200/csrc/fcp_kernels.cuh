@@ -292,7 +292,15 @@ struct Args {
   const uint8_t* const* slice_base = nullptr;  // device array, or nullptr
   uint32_t slice_regions = 0;
   uint64_t rotate = 0;  // sliced scatter: run index this launch starts from
+  // kFusedFinalize: the last warp to leave also combines the region values
+  // of chunks [chunk_begin, chunk_end) into chunk_sums (small images: saves
+  // the separate finalize launch)
+  uint32_t* chunk_sums = nullptr;
+  uint32_t regions_per_chunk = 0;
+  uint64_t chunk_begin = 0, chunk_end = 0;
 };
 constexpr uint32_t kNoPrefetch = 1u;
+constexpr uint32_t kFusedFinalize = 2u;
+constexpr uint64_t kFuseMaxChunks = 2;  // the last warp combines them one after the other: 32 cost 40 us
 
 }  // namespace fcpk

@@ -131,6 +131,56 @@ __device__ __forceinline__ void store_some_bytes(uintptr_t t, const W8& w, int f
                         from, n);
 }
 
+// shift a raw CRC state by n regions of zeros (binary decomposition of n over
+// the 2^j-region tables)
+__device__ __forceinline__ uint32_t shift_regions(uint32_t x, uint32_t n) {
+  for (int j = 0; n != 0u; ++j, n >>= 1)
+    if (n & 1u) x = lin4(g_fcp_tab_regions + j * 1024, x);
+  return x;
+}
+
+// One WARP combines the region values of chunk c into the raw CRC of the
+// chunk (its last region zero-padded to 16 KiB; the host strips that padding
+// and applies init/xorout, fcp_finish_checksums).  Lane l owns up to
+// q = ceil(regions_per_chunk / 32) consecutive regions, right-aligned so that
+// lane 31 owns the chunk's last ones (empty leading lanes contribute the raw
+// CRC of nothing, 0, which no shift changes); q Horner steps, then a 5-level
+// tree.  Region values are read from L2 (ld.cg): in the fused form they were
+// written by other SMs of the same launch.
+__device__ __forceinline__ void combine_chunk(const uint32_t* __restrict__ region_sums,
+                                              uint32_t* __restrict__ chunk_sums,
+                                              uint64_t n_regions, uint32_t regions_per_chunk,
+                                              uint64_t c, int lane) {
+  const uint64_t r0 = c * regions_per_chunk;
+  uint64_t r1 = r0 + regions_per_chunk;
+  if (r1 > n_regions) r1 = n_regions;
+  const int64_t n = static_cast<int64_t>(r1 - r0);
+  const int64_t q = (static_cast<int64_t>(regions_per_chunk) + 31) / 32;
+  int64_t hi = n - static_cast<int64_t>(31 - lane) * q;
+  int64_t lo = hi - q;
+  if (hi < 0) hi = 0;
+  if (lo < 0) lo = 0;
+  uint32_t acc = 0;
+  const uint32_t* one = g_fcp_tab_regions;  // shift by one region
+  int64_t j = lo;
+  for (; j + 4 <= hi; j += 4) {  // values first: they do not depend on acc
+    uint32_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = __ldcg(region_sums + r0 + j + k);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc = lin4(one, acc) ^ v[k];
+  }
+  for (; j < hi; ++j) acc = lin4(one, acc) ^ __ldcg(region_sums + r0 + j);
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const uint32_t recv = __shfl_up_sync(0xffffffffu, acc, 1u << k);
+    const uint32_t sh = shift_regions(recv, static_cast<uint32_t>(q) << k);
+    const uint32_t m = (2u << k) - 1u;
+    if ((static_cast<uint32_t>(lane) & m) == m) acc ^= sh;
+  }
+  if (lane == 31) chunk_sums[c] = acc;
+}
+
 // ---------------------------------------------------------------- the kernel
 // PACK = true : tensors -> packed image   (desc.ptr is the source)
 // PACK = false: packed image -> tensors   (desc.ptr is the target)
@@ -381,9 +431,28 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
   // The last warp to leave resets the counters, so launches that follow on
   // the same stream find them at zero (a.work[1] counts departed warps; a
   // warp increments it only after its final draw).
-  if (work != nullptr && lane == 0) {
-    const uint32_t gone = atomicAdd(&work[1], 1u);
-    if (gone == static_cast<uint32_t>(warps_total) - 1u) {
+  if (work != nullptr) {
+    bool last = false;
+    if (THREADS < 1024 && CRC && (a.flags & kFusedFinalize)) {
+      __threadfence();  // this warp's region values are visible before it signs off
+      __syncwarp();
+    }
+    if (lane == 0) {
+      const uint32_t gone = atomicAdd(&work[1], 1u);
+      last = gone == static_cast<uint32_t>(warps_total) - 1u;
+    }
+    if (THREADS < 1024 && CRC && (a.flags & kFusedFinalize)) {
+      // small image: the last warp out combines the chunks itself instead of
+      // a second launch (every other warp has fenced its values and left)
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (last) {
+        __threadfence();
+        const uint64_t n_regions = (total + kRegion - 1) / kRegion;
+        for (uint64_t c = a.chunk_begin; c < a.chunk_end; ++c)
+          combine_chunk(a.region_sums, a.chunk_sums, n_regions, a.regions_per_chunk, c, lane);
+      }
+    }
+    if (lane == 0 && last) {
       work[0] = 0u;
       work[1] = 0u;
     }
@@ -490,57 +559,15 @@ __global__ void __launch_bounds__(128) fcp_xxh64_kernel(const uint8_t* __restric
   out[chunk] = h;
 }
 
-// shift a raw CRC state by n regions of zeros (binary decomposition of n over
-// the 2^j-region tables)
-__device__ __forceinline__ uint32_t shift_regions(uint32_t x, uint32_t n) {
-  for (int j = 0; n != 0u; ++j, n >>= 1)
-    if (n & 1u) x = lin4(g_fcp_tab_regions + j * 1024, x);
-  return x;
-}
-
-// One WARP per chunk: combines the chunk's region values into the raw CRC of
-// the chunk (its last region zero-padded to 16 KiB; the host strips that
-// padding and applies init/xorout, fcp_finish_checksums).  Lane l owns up to
-// q = ceil(regions_per_chunk / 32) consecutive regions, right-aligned so that
-// lane 31 owns the chunk's last ones (empty leading lanes contribute the raw
-// CRC of nothing, 0, which no shift changes); q Horner steps, then a 5-level
-// tree.  One thread per chunk walked 128 dependent table lookups (17 us,
-// the floor of every small image).
+// One warp per chunk (it was one thread walking 128 dependent table lookups:
+// 17 us, the floor of every small image).
 __global__ void __launch_bounds__(128) fcp_finalize_kernel(
     const uint32_t* __restrict__ region_sums, uint32_t* __restrict__ chunk_sums,
     uint64_t n_regions, uint32_t regions_per_chunk, uint64_t chunk_begin, uint64_t chunk_end) {
-  const int lane = threadIdx.x & 31;
   const uint64_t c = chunk_begin + blockIdx.x * static_cast<uint64_t>(blockDim.x >> 5) +
                      (threadIdx.x >> 5);
   if (c >= chunk_end) return;  // uniform across the warp
-  const uint64_t r0 = c * regions_per_chunk;
-  uint64_t r1 = r0 + regions_per_chunk;
-  if (r1 > n_regions) r1 = n_regions;
-  const int64_t n = static_cast<int64_t>(r1 - r0);
-  const int64_t q = (static_cast<int64_t>(regions_per_chunk) + 31) / 32;
-  int64_t hi = n - static_cast<int64_t>(31 - lane) * q;
-  int64_t lo = hi - q;
-  if (hi < 0) hi = 0;
-  if (lo < 0) lo = 0;
-  uint32_t acc = 0;
-  const uint32_t* one = g_fcp_tab_regions;  // shift by one region
-  int64_t j = lo;
-  for (; j + 4 <= hi; j += 4) {  // values first: they do not depend on acc
-    uint32_t v[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) v[k] = __ldg(region_sums + r0 + j + k);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) acc = lin4(one, acc) ^ v[k];
-  }
-  for (; j < hi; ++j) acc = lin4(one, acc) ^ __ldg(region_sums + r0 + j);
-#pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    const uint32_t recv = __shfl_up_sync(0xffffffffu, acc, 1u << k);
-    const uint32_t sh = shift_regions(recv, static_cast<uint32_t>(q) << k);
-    const uint32_t m = (2u << k) - 1u;
-    if ((static_cast<uint32_t>(lane) & m) == m) acc ^= sh;
-  }
-  if (lane == 31) chunk_sums[c] = acc;
+  combine_chunk(region_sums, chunk_sums, n_regions, regions_per_chunk, c, threadIdx.x & 31);
 }
 
 }  // namespace fcpk

@@ -276,7 +276,8 @@ int fcp_restore_from_device(fcp_plan* plan, const void* packed, int checksum,
  * at slice `first_slice` and wraps around: give every rank of the group a
  * different one (its own index + 1) so that at any moment the ranks read
  * different peers instead of all draining one peer's NVLink egress
- * (measured, 8 ranks: 174 -> see DESIGN.md §6).  Synchronous.              */
+ * (measured, 8 ranks, all-to-all: 174 GB/s into each GPU with a common
+ * start, 405 GB/s rotated).  Synchronous.                                  */
 int fcp_restore_from_slices(fcp_plan* plan, const void* const* slice_bases,
                             uint64_t n_slices, uint64_t slice_bytes,
                             int checksum, const uint32_t* expected,
