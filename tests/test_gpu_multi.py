@@ -265,15 +265,15 @@ def _fsdp_worker(rank, world, port, run_id, tmpdir, errq):
         raise
 
 
-def _run_two_ranks(worker, tag):
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+def _run_two_ranks(worker, tag, world=2):
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (run with gpurun --gpus %d)" % (world, world))
     ctx = mp.get_context("spawn")
     errq = ctx.SimpleQueue()
-    port, run_id = _free_port(), "fcp_gpu2_%s_%d" % (tag, os.getpid())
+    port, run_id = _free_port(), "fcp_gpu%d_%s_%d" % (world, tag, os.getpid())
     with tempfile.TemporaryDirectory() as tmpdir:
-        procs = [ctx.Process(target=worker, args=(r, 2, port, run_id, tmpdir, errq))
-                 for r in range(2)]
+        procs = [ctx.Process(target=worker, args=(r, world, port, run_id, tmpdir, errq))
+                 for r in range(world)]
         for p in procs:
             p.start()
         for p in procs:
@@ -291,6 +291,14 @@ def _run_two_ranks(worker, tag):
 @pytest.mark.timeout(300)
 def test_two_rank_fsdp_sharded_cached_plan_and_async():
     _run_two_ranks(_fsdp_worker, "fsdp")
+
+
+@pytest.mark.timeout(300)
+def test_one_rank_fsdp_checkpointer_cached_plan_and_async():
+    """The same through FsdpCheckpointer with a world of one rank (NCCL), so
+    that a 1-GPU box also exercises the FSDP engine on CUDA: planned save,
+    cached-plan saves (sync and async), restore through the scatter kernel."""
+    _run_two_ranks(_fsdp_worker, "fsdp1", world=1)
 
 
 @pytest.mark.timeout(300)
