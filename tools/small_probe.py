@@ -61,7 +61,11 @@ def main():
     print("| tensors | size | layout | B (MB) | pack+CRC ms | GB/s (2B) | scatter+CRC ms | GB/s (2B) "
           "| pack GPU-only ms | scatter GPU-only ms |")
     print("|---|---|---|---|---|---|---|---|---|---|")
-    for n, size, adamw in CELLS:
+    cells = CELLS
+    for arg in sys.argv[1:]:
+        if arg.startswith("--cells="):  # e.g. --cells=4,6 (indices into CELLS)
+            cells = [CELLS[int(i)] for i in arg.split("=", 1)[1].split(",")]
+    for n, size, adamw in cells:
         sd = build(n, size, adamw)
         flat, meta, total = oracle.flatten(sd)
         descs = _native.make_descs([t.data_ptr() for t, m in flat], [m.offset for t, m in flat],
