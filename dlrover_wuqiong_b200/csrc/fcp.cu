@@ -84,7 +84,7 @@ int init_device(int dev) {
                               sizeof(uint32_t) * fcpk::kTabWords));
   std::vector<uint32_t> reg(fcpk::kRegionShiftTabs * 1024);
   for (int j = 0; j < fcpk::kRegionShiftTabs; ++j)
-    fcpcrc::make_table(fcpcrc::shift_bytes(static_cast<uint64_t>(fcpk::kRegion) << j),
+    fcpcrc::make_table(fcpcrc::shift_bytes(static_cast<uint64_t>(fcpk::kUnitBytes) << j),
                        &reg[j * 1024]);
   FCP_CUDA(cudaMemcpyToSymbol(fcpk::g_fcp_tab_regions, reg.data(),
                               sizeof(uint32_t) * reg.size()));
@@ -120,7 +120,8 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_
   // the big grid a region: 256-thread CTAs, unreplicated tables.
   static const bool force_big = getenv("FCP_DEBUG_FORCE_BIG") != nullptr;  // tuning aid
   const uint64_t runs = ceil_div(regions, a.run);
-  const bool big = (CRC || force_big) && runs >= static_cast<uint64_t>(sms) * 32;
+  const bool fine = !SLICED && (a.flags & fcpk::kFineUnits) != 0;  // 4 KiB units: small shape
+  const bool big = !fine && (CRC || force_big) && runs >= static_cast<uint64_t>(sms) * 32;
   // the last-warp-out finalize exists in the 256-thread shape only, needs the
   // plan's counters and a checksum
   if (big || !CRC || a.work == nullptr) a.flags &= ~fcpk::kFusedFinalize;
@@ -150,11 +151,18 @@ int launch_dir(const fcpk::Args& a_in, int dev, cudaStream_t st, uint64_t first_
     }
     kern<<<sms, kBigThreads, kSmemBig, st>>>(a);
   } else {
-    auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads, SLICED>;
     const uint64_t want = ceil_div(runs, kSmallThreads / 32);
-    const uint64_t cap = static_cast<uint64_t>(sms) * 8;
+    static const int per_sm = getenv("FCP_DEBUG_SMALL_CTAS_PER_SM")
+                                  ? atoi(getenv("FCP_DEBUG_SMALL_CTAS_PER_SM")) : 8;  // tuning aid
+    const uint64_t cap = static_cast<uint64_t>(sms) * (per_sm > 0 ? per_sm : 8);
     const unsigned grid = static_cast<unsigned>(want < cap ? want : cap);
-    kern<<<grid, kSmallThreads, CRC ? kSmemSmall : 0, st>>>(a);
+    if (fine) {
+      auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads, false, fcpk::kFineRows>;
+      kern<<<grid, kSmallThreads, CRC ? kSmemSmall : 0, st>>>(a);
+    } else {
+      auto kern = fcpk::fcp_kernel<PACK, CRC, 1, kSmallThreads, SLICED>;
+      kern<<<grid, kSmallThreads, CRC ? kSmemSmall : 0, st>>>(a);
+    }
   }
   FCP_CUDA(cudaGetLastError());
   return 0;
@@ -175,16 +183,26 @@ int launch_any(const fcpk::Args& a, int direction, int checksum, int dev,
                   : launch_dir<false, false>(a, dev, st, 0, fused);
 }
 
+// `n_regions` / `regions_per_chunk` count 16 KiB regions; with fine = true the
+// values in region_sums are those of 4 KiB units of an image of `total` bytes
 int launch_finalize(const uint32_t* region_sums, uint32_t* chunk_sums,
                     uint64_t n_regions, uint32_t regions_per_chunk,
-                    uint64_t chunk_begin, uint64_t chunk_end, cudaStream_t st) {
+                    uint64_t chunk_begin, uint64_t chunk_end, cudaStream_t st,
+                    bool fine = false, uint64_t total = 0) {
   const uint64_t nc = chunk_end - chunk_begin;
   if (nc == 0) return 0;
   const unsigned threads = 128;  // one warp per chunk
   const unsigned grid = static_cast<unsigned>(ceil_div(nc, threads / 32));
-  fcpk::fcp_finalize_kernel<<<grid, threads, 0, st>>>(
-      region_sums, chunk_sums, n_regions, regions_per_chunk, chunk_begin,
-      chunk_end);
+  if (fine) {
+    const uint64_t per = FCP_REGION_BYTES / fcpk::kUnitBytes;
+    fcpk::fcp_finalize_kernel<<<grid, threads, 0, st>>>(
+        region_sums, chunk_sums, ceil_div(total, fcpk::kUnitBytes), n_regions * per,
+        static_cast<uint32_t>(regions_per_chunk * per), chunk_begin, chunk_end, 0);
+  } else {
+    fcpk::fcp_finalize_kernel<<<grid, threads, 0, st>>>(
+        region_sums, chunk_sums, n_regions, n_regions, regions_per_chunk, chunk_begin,
+        chunk_end, fcpk::kCoarseUnitLog);
+  }
   FCP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -229,6 +247,7 @@ struct fcp_plan {
   bool last_has_sums = false;
   bool save_in_flight = false;
   int save_mode = 0;
+  bool fine = false;  // small image: kernels work in 4 KiB units (4x the warps)
   uint64_t win_begin = 0, win_end = ~0ull;  // chunk window of fcp_save_async
   // staged save whose device->host copies are enqueued apart from the pack
   bool defer_copies = false, copies_pending = false;
@@ -286,6 +305,12 @@ fcpk::Args plan_args(const fcp_plan* p, void* packed, uint64_t rb, uint64_t re) 
   return a;
 }
 
+// chunk values of chunks [cb, ce) from the values the plan's launches left
+int plan_finalize(fcp_plan* p, uint64_t cb, uint64_t ce, cudaStream_t st) {
+  return launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
+                         p->chunk_bytes / FCP_REGION_BYTES, cb, ce, st, p->fine, p->total);
+}
+
 // kernels for chunks [cb, ce) of the plan, on stream st; `finalize` = also
 // combine the region values of those chunks into chunk values
 int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
@@ -296,10 +321,19 @@ int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
   bool fused = false;
   if (re > rb) {
     fcpk::Args a = plan_args(p, packed, rb, re);
+    uint32_t per_chunk = rpc;
+    if (p->fine) {  // the same range in 4 KiB units
+      const uint64_t per = FCP_REGION_BYTES / fcpk::kUnitBytes;
+      const uint64_t n_units = ceil_div(p->total, fcpk::kUnitBytes);
+      a.flags |= fcpk::kFineUnits;
+      a.region_begin = rb * per;
+      a.region_end = re * per < n_units ? re * per : n_units;
+      per_chunk = static_cast<uint32_t>(rpc * per);
+    }
     if (checksum && finalize && ce - cb <= fcpk::kFuseMaxChunks) {
       a.flags |= fcpk::kFusedFinalize;  // (kept only for the small shape, see launch_dir)
       a.chunk_sums = p->d_chunk_sums;
-      a.regions_per_chunk = rpc;
+      a.regions_per_chunk = per_chunk;
       a.chunk_begin = cb;
       a.chunk_end = ce < p->n_chunks ? ce : p->n_chunks;
     }
@@ -308,8 +342,7 @@ int plan_launch(fcp_plan* p, void* packed, int direction, int checksum,
     p->last_launches++;
   }
   if (checksum && finalize && ce > cb && !fused) {
-    int rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
-                             rpc, cb, ce, st);
+    int rc = plan_finalize(p, cb, ce, st);
     if (rc) return rc;
     p->last_launches++;
   }
@@ -439,8 +472,14 @@ int fcp_plan_create(const fcp_desc* descs, uint64_t n, uint64_t total_bytes,
   FCP_TRY(cudaMalloc(&p->d_descs, sizeof(fcp_desc) * (n ? n : 1)));
   FCP_TRY(cudaMallocHost(&p->h_pinned, sizeof(fcp_desc) * (n ? n : 1)));
   FCP_TRY(cudaEventCreateWithFlags(&p->ev_upload, cudaEventDisableTiming));
+  // one value per 4 KiB unit: room for the fine work unit of small images
   FCP_TRY(cudaMalloc(&p->d_region_sums,
-                     sizeof(uint32_t) * (p->n_regions ? p->n_regions : 1)));
+                     sizeof(uint32_t) * (FCP_REGION_BYTES / fcpk::kUnitBytes) *
+                         (p->n_regions ? p->n_regions : 1)));
+  // images too small to give every warp of a full 1024-thread grid a region
+  // are worked in 4 KiB units by the 256-thread shape (4x the warps)
+  p->fine = p->n_regions < static_cast<uint64_t>(g_sm_count[device] > 0 ? g_sm_count[device] : 148) * 32 &&
+            getenv("FCP_DEBUG_COARSE") == nullptr;
   FCP_TRY(cudaMalloc(&p->d_chunk_sums,
                      sizeof(uint32_t) * (p->n_chunks ? p->n_chunks : 1)));
   FCP_TRY(cudaMalloc(&p->d_work, 256));
@@ -830,8 +869,7 @@ int fcp_save_async(fcp_plan* p, void* staging, void* host_dst, int mode,
     const uint64_t wb = p->win_begin < p->n_chunks ? p->win_begin : p->n_chunks;
     const uint64_t we = p->win_end < p->n_chunks ? p->win_end : p->n_chunks;
     if (checksum && we > wb) {
-      rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
-                           p->chunk_bytes / FCP_REGION_BYTES, wb, we, st);
+      rc = plan_finalize(p, wb, we, st);
       if (rc) return rc;
       p->last_launches++;
     }
@@ -956,8 +994,7 @@ int fcp_restore(fcp_plan* p, const void* host_src, void* staging, int mode,
       if (rc) return rc;
     }
     if (checksum && p->n_chunks) {
-      rc = launch_finalize(p->d_region_sums, p->d_chunk_sums, p->n_regions,
-                           p->chunk_bytes / FCP_REGION_BYTES, 0, p->n_chunks, st);
+      rc = plan_finalize(p, 0, p->n_chunks, st);
       if (rc) return rc;
       p->last_launches++;
     }

@@ -35,9 +35,15 @@ constexpr int kTabK = 1024;         // shift 992 B (row stride - word)
 constexpr int kTabC = 2048;         // 5 tables: shift 32,64,128,256,512 B
 constexpr int kTabF = 2048 + 5120;  // shift one region (16 KiB)
 constexpr int kTabWords = kTabF + 1024;
-// shift by 2^j regions, j = 0 .. kRegionShiftTabs-1 (chunk_bytes is a uint32:
-// at most 2^18 regions per chunk); used by the chunk finaliser
-constexpr int kRegionShiftTabs = 19;
+// shift by 2^j work units of 4 KiB, j = 0 .. kRegionShiftTabs-1 (chunk_bytes is
+// a uint32: at most 2^20 such units per chunk); used by the chunk finaliser.
+// A 16 KiB region is 2^2 units (kCoarseUnitLog); images too small to give every
+// warp of a full grid a region are worked in 4 KiB units instead (kFineRows
+// rows per warp visit: four times the warps, see profiles/r02_small_images.md).
+constexpr int kRegionShiftTabs = 21;
+constexpr int kUnitBytes = 4096;
+constexpr int kFineRows = 4;
+constexpr int kCoarseUnitLog = 2;
 
 // per-device constant tables, filled once by fcp_init()
 static __device__ __align__(16) uint32_t g_fcp_tab[kTabWords];
@@ -301,6 +307,7 @@ struct Args {
 };
 constexpr uint32_t kNoPrefetch = 1u;
 constexpr uint32_t kFusedFinalize = 2u;
+constexpr uint32_t kFineUnits = 4u;  // region_begin/end and region_sums count 4 KiB units
 constexpr uint64_t kFuseMaxChunks = 2;  // the last warp combines them one after the other: 32 cost 40 us
 
 }  // namespace fcpk

@@ -133,8 +133,8 @@ __device__ __forceinline__ void store_some_bytes(uintptr_t t, const W8& w, int f
 
 // shift a raw CRC state by n regions of zeros (binary decomposition of n over
 // the 2^j-region tables)
-__device__ __forceinline__ uint32_t shift_regions(uint32_t x, uint32_t n) {
-  for (int j = 0; n != 0u; ++j, n >>= 1)
+__device__ __forceinline__ uint32_t shift_regions(uint32_t x, uint32_t n, int unit_log) {
+  for (int j = unit_log; n != 0u; ++j, n >>= 1)
     if (n & 1u) x = lin4(g_fcp_tab_regions + j * 1024, x);
   return x;
 }
@@ -147,13 +147,17 @@ __device__ __forceinline__ uint32_t shift_regions(uint32_t x, uint32_t n) {
 // CRC of nothing, 0, which no shift changes); q Horner steps, then a 5-level
 // tree.  Region values are read from L2 (ld.cg): in the fused form they were
 // written by other SMs of the same launch.
+// `unit_log`: the values are those of 4 KiB << unit_log work units; `n_real`
+// of them exist, and the chunk is taken as zero-padded up to `n_padded` units
+// (the end of the image's last 16 KiB region, whatever the unit).
 __device__ __forceinline__ void combine_chunk(const uint32_t* __restrict__ region_sums,
                                               uint32_t* __restrict__ chunk_sums,
-                                              uint64_t n_regions, uint32_t regions_per_chunk,
-                                              uint64_t c, int lane) {
+                                              uint64_t n_real, uint64_t n_padded,
+                                              uint32_t regions_per_chunk, uint64_t c, int lane,
+                                              int unit_log) {
   const uint64_t r0 = c * regions_per_chunk;
   uint64_t r1 = r0 + regions_per_chunk;
-  if (r1 > n_regions) r1 = n_regions;
+  if (r1 > n_padded) r1 = n_padded;
   const int64_t n = static_cast<int64_t>(r1 - r0);
   const int64_t q = (static_cast<int64_t>(regions_per_chunk) + 31) / 32;
   int64_t hi = n - static_cast<int64_t>(31 - lane) * q;
@@ -161,20 +165,22 @@ __device__ __forceinline__ void combine_chunk(const uint32_t* __restrict__ regio
   if (hi < 0) hi = 0;
   if (lo < 0) lo = 0;
   uint32_t acc = 0;
-  const uint32_t* one = g_fcp_tab_regions;  // shift by one region
+  const uint32_t* one = g_fcp_tab_regions + unit_log * 1024;  // shift by one unit
   int64_t j = lo;
   for (; j + 4 <= hi; j += 4) {  // values first: they do not depend on acc
     uint32_t v[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) v[k] = __ldcg(region_sums + r0 + j + k);
+    for (int k = 0; k < 4; ++k)
+      v[k] = r0 + j + k < n_real ? __ldcg(region_sums + r0 + j + k) : 0u;
 #pragma unroll
     for (int k = 0; k < 4; ++k) acc = lin4(one, acc) ^ v[k];
   }
-  for (; j < hi; ++j) acc = lin4(one, acc) ^ __ldcg(region_sums + r0 + j);
+  for (; j < hi; ++j)
+    acc = lin4(one, acc) ^ (r0 + j < n_real ? __ldcg(region_sums + r0 + j) : 0u);
 #pragma unroll
   for (int k = 0; k < 5; ++k) {
     const uint32_t recv = __shfl_up_sync(0xffffffffu, acc, 1u << k);
-    const uint32_t sh = shift_regions(recv, static_cast<uint32_t>(q) << k);
+    const uint32_t sh = shift_regions(recv, static_cast<uint32_t>(q) << k, unit_log);
     const uint32_t m = (2u << k) - 1u;
     if ((static_cast<uint32_t>(lane) & m) == m) acc ^= sh;
   }
@@ -189,8 +195,13 @@ __device__ __forceinline__ void combine_chunk(const uint32_t* __restrict__ regio
 // SLICED: the image is read through Args.slice_base (scatter from several
 // buffers); a separate instantiation so the ordinary kernels keep their
 // register budget.
-template <bool PACK, bool CRC, int REPL, int THREADS, bool SLICED = false>
+// ROWS: rows (KiB) of the image one warp visit covers: 16 = a region; 4 = the
+// fine unit of small images (Args.region_begin/end and region_sums then count
+// 4 KiB units; same code, a quarter of the rows).
+template <bool PACK, bool CRC, int REPL, int THREADS, bool SLICED = false, int ROWS = 16>
 __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
+  constexpr int kRows = ROWS;                 // (shadow the 16-row constants
+  constexpr int kRegion = kRowBytes * ROWS;   //  of the namespace)
   constexpr int RK = REPL > 1 ? REPL / 2 : 1;
   constexpr int kBatch = FCP_ALIGNED_BATCH;
   extern __shared__ uint32_t smem[];
@@ -447,9 +458,12 @@ __global__ void __launch_bounds__(THREADS, 1) fcp_kernel(const Args a) {
       last = __shfl_sync(0xffffffffu, last, 0);
       if (last) {
         __threadfence();
-        const uint64_t n_regions = (total + kRegion - 1) / kRegion;
+        const uint64_t n_real = (total + kRegion - 1) / kRegion;
+        const uint64_t n_padded =
+            (total + FCP_REGION_BYTES - 1) / FCP_REGION_BYTES * (FCP_REGION_BYTES / kRegion);
         for (uint64_t c = a.chunk_begin; c < a.chunk_end; ++c)
-          combine_chunk(a.region_sums, a.chunk_sums, n_regions, a.regions_per_chunk, c, lane);
+          combine_chunk(a.region_sums, a.chunk_sums, n_real, n_padded, a.regions_per_chunk, c,
+                        lane, ROWS == 16 ? kCoarseUnitLog : 0);
       }
     }
     if (lane == 0 && last) {
@@ -563,11 +577,13 @@ __global__ void __launch_bounds__(128) fcp_xxh64_kernel(const uint8_t* __restric
 // 17 us, the floor of every small image).
 __global__ void __launch_bounds__(128) fcp_finalize_kernel(
     const uint32_t* __restrict__ region_sums, uint32_t* __restrict__ chunk_sums,
-    uint64_t n_regions, uint32_t regions_per_chunk, uint64_t chunk_begin, uint64_t chunk_end) {
+    uint64_t n_real, uint64_t n_padded, uint32_t regions_per_chunk, uint64_t chunk_begin,
+    uint64_t chunk_end, int unit_log) {
   const uint64_t c = chunk_begin + blockIdx.x * static_cast<uint64_t>(blockDim.x >> 5) +
                      (threadIdx.x >> 5);
   if (c >= chunk_end) return;  // uniform across the warp
-  combine_chunk(region_sums, chunk_sums, n_regions, regions_per_chunk, c, threadIdx.x & 31);
+  combine_chunk(region_sums, chunk_sums, n_real, n_padded, regions_per_chunk, c,
+                threadIdx.x & 31, unit_log);
 }
 
 }  // namespace fcpk
