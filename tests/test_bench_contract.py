@@ -51,3 +51,29 @@ def test_product_arm_fails_loudly_without_cuda():
     assert out.returncode != 0
     assert not [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
     assert "CUDA" in out.stderr or "cuda" in out.stderr
+
+
+def test_reference_arm_under_torchrun_runs_on_every_rank():
+    """N > 1: the driver launches the reference arm with torchrun like the
+    product arm; every rank runs the reference's path on its own shard at the
+    same time (gloo for the barriers) and rank 0 prints the one line."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    out = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+         "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "bench.py"),
+         "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1",
+         "--workload", "gpt2-small-124M-adamw-fp32"],
+        capture_output=True, text=True, cwd=ROOT, env=env, timeout=900)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, out.stdout[-2000:]
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["config"]["ranks"] == 2
+    assert d["config"]["same_config"] is True and d["value"] > 0
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
